@@ -1,0 +1,150 @@
+/* ddpmnist_b200.h — C ABI of libddpmnist_b200.so
+ *
+ * B200 (sm_100a) implementation of ONE hot path: the data-parallel MNIST training step of
+ * Jonathanlyj/pytorch_ddp_mnist, `mnist_pnetcdf_cpu_mp.py` ("mp:" below).  The reference has no
+ * FFI/plugin seam (it is pure Python on top of torch); each entry point therefore cites the
+ * reference statement(s) whose work it performs, and INTEGRATION.md shows the ctypes binding a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain C types only; every pointer named d_* is a DEVICE pointer owned by the caller
+ *     (PyTorch tensors in practice), h_* is a HOST pointer.  The library allocates no device
+ *     memory and keeps no pointer after a call returns.
+ *   - every GPU entry point is asynchronous and ordered on `stream` (a cudaStream_t passed as
+ *     void*; NULL = legacy default stream); none of them synchronises or allocates, so they can be
+ *     captured in a CUDA graph.
+ *   - return value: 0 = ok, non-zero = error; ddpm_last_error() returns a thread-local message.
+ *   - flat parameter layout (118,272 fp32 = 473,088 B, the reference's single DDP bucket), in
+ *     `model.parameters()` order, each matrix row-major [out,in] (mp:412-422):
+ *         W1 [128,784] @ 0 | b1 [128] @ 100352 | W2 [128,128] @ 100480 | b2 [128] @ 116864 |
+ *         W3 [10,128] @ 116992
+ *     gradients use the same layout.
+ *   - indices are int64 (what torch's samplers produce); labels are uint8 (what the reference's
+ *     loader yields, mp:45-49).
+ */
+#ifndef DDPMNIST_B200_H
+#define DDPMNIST_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPM_IN        784
+#define DDPM_HID       128
+#define DDPM_CLASSES   10
+#define DDPM_N_PARAMS  118272
+#define DDPM_OFF_W1    0
+#define DDPM_OFF_B1    100352
+#define DDPM_OFF_W2    100480
+#define DDPM_OFF_B2    116864
+#define DDPM_OFF_W3    116992
+
+/* -------------------------------------------------------------------------------- misc */
+const char* ddpm_last_error(void);
+/* ABI version of this header; bumped on any signature change. */
+int ddpm_abi_version(void);
+/* Fills the 256-entry decode table on the host with the same arithmetic the kernels use:
+ * fp32 IEEE  ((v / 255) - 0.1307f) / 0.3081f   — ToTensor + Normalize, mp:374-377. */
+int ddpm_decode_lut_host(float* h_lut256);
+
+/* -------------------------------------------------------------------------------- loader
+ * K1. Replaces B calls of MNISTNetCDF.__getitem__ + default_collate + x.view(B,-1)
+ * (mp:39-49, mp:454, mp:458) for a dataset that is resident in HBM.
+ *   d_images  u8 [n_samples,784] (row i = the 784 bytes at begin_images + 784*i of the CDF-5 file)
+ *   d_labels  u8 [n_samples]
+ *   d_idx     i64[batch]  sample indices (a slice of the DistributedSampler shard, mp:390-394)
+ *   d_x       f32[batch,784] out, bit-exact with the reference's transform stack
+ *   d_y       u8 [batch] out
+ * Fails (returns non-zero) on batch < 0 / n_samples <= 0; indices are range-checked on the
+ * device: an out-of-range index writes NaN rows and sets *d_status (i32, may be NULL) to 1. */
+int ddpm_gather_decode(const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                       const int64_t* d_idx, int batch, float* d_x, uint8_t* d_y,
+                       int* d_status, void* stream);
+
+/* K7. Dropout keep-mask for nn.Dropout(0.2) (mp:417), perf mode: Philox4x32-10 keyed by `seed`,
+ * counter = (step, element/4).  d_mask u8[batch,128] in {0,1}, P(1) = 0.8.  Parity mode does not
+ * call this: the caller supplies the oracle's mask. */
+int ddpm_dropout_mask_philox(uint8_t* d_mask, int batch, uint64_t seed, uint64_t step, void* stream);
+
+/* -------------------------------------------------------------------------------- fused step
+ * Workspace: one caller-owned device buffer of ddpm_workspace_bytes(max_batch) bytes, 256-byte
+ * aligned, reused by every step (activations, gates, split-K partials, two control words).
+ * Call ddpm_workspace_init once after allocating it (it zeroes the control words; stream-ordered).
+ * Contents between calls are meaningful only to ddpm_step_backward, which reads what the last
+ * ddpm_step_forward on the same workspace left.  One workspace serves one stream at a time. */
+size_t ddpm_workspace_bytes(int max_batch);
+int    ddpm_workspace_init(void* d_workspace, int max_batch, void* stream);
+
+#define DDPM_FWD_PREP_BACKWARD 1u  /* also compute dL/dz2, dL/dz1 from the CE gradient (training) */
+#define DDPM_FWD_PHILOX_MASK   2u  /* draw the dropout mask in-kernel (seed, step); d_mask unused */
+
+/* Forward of create_model() + CrossEntropyLoss (mp:412-422, mp:460-461; eval form mp:476-477).
+ * Input rows come either from the resident u8 dataset through d_idx (d_x == NULL; the decode is
+ * fused into the fc1 operand load) or from an fp32 batch d_x[batch,784] (d_images/d_idx unused).
+ *   d_params   f32[118272]
+ *   d_mask     u8[batch,128] dropout keep mask; NULL (and no PHILOX flag) = eval mode
+ *              (model.eval(), mp:470: dropout is the identity)
+ *   d_y        u8[batch] labels; if NULL and d_idx is given, labels are gathered from d_labels;
+ *              if no labels are available the loss outputs are not written
+ *   d_logits   f32[batch,10] out (may be NULL)
+ *   d_loss     f32[2] (may be NULL): [0] = mean loss of this batch (nn.CrossEntropyLoss default);
+ *              [1] += loss/batch — the reference's epoch bookkeeping `epoch_loss += batch_loss /
+ *              x.shape[0]` (mp:465, 481) accumulated on the device, so no per-step host sync is
+ *              needed; the caller zeroes d_loss[1] at the start of an epoch. */
+int ddpm_step_forward(const float* d_params,
+                      const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                      const int64_t* d_idx, const float* d_x, const uint8_t* d_y,
+                      const uint8_t* d_mask, uint64_t philox_seed, uint64_t philox_step,
+                      int batch, unsigned flags,
+                      float* d_logits, float* d_loss, void* d_workspace, void* stream);
+
+/* Backward of the same step (batch_loss.backward(), mp:462) for the batch last given to
+ * ddpm_step_forward with this workspace (same d_images/d_idx/d_x must be passed again: the input
+ * is re-decoded for the fc1 weight gradient instead of being stored).
+ * Writes dL/dparams into d_grads f32[118272] (may be NULL when lr != 0) scaled by grad_scale
+ * (1/world_size folds DDP's pre-division, c10d reducer semantics behind mp:439; 1.0 otherwise).
+ * If d_dlogits != NULL it is used as dL/dlogits f32[batch,10] (autograd path: any upstream loss);
+ * otherwise the forward must have been called with DDPM_FWD_PREP_BACKWARD.
+ * If lr != 0 the SGD update p <- fma(-lr, g, p) (optimizer.step(), mp:463) is fused into the
+ * gradient epilogue (single-GPU fast path; d_params is written). */
+int ddpm_step_backward(float* d_params,
+                       const uint8_t* d_images, int64_t n_samples,
+                       const int64_t* d_idx, const float* d_x,
+                       const float* d_dlogits, int batch, float grad_scale, float lr,
+                       float* d_grads, void* d_workspace, void* stream);
+
+/* K4 alone. nn.CrossEntropyLoss()(logits, y) forward + gradient (mp:444, 461): d_loss[0] = mean
+ * NLL of log_softmax; d_dlogits = (softmax - onehot)/batch (may be NULL).  y is uint8. */
+int ddpm_cross_entropy(const float* d_logits, const uint8_t* d_y, int batch,
+                       float* d_loss, float* d_dlogits, void* stream);
+
+/* -------------------------------------------------------------------------------- optimizer
+ * K6. optim.SGD(lr).step() over the flat buffer (mp:443, 463; torch/optim/sgd.py
+ * `param.add_(grad, alpha=-lr)`): p[i] = fma(-lr, grad_scale * g[i], p[i]).  With grad_scale == 1
+ * this is bit-exact with the reference's update. */
+int ddpm_sgd_step(float* d_params, const float* d_grads, int64_t n, float lr, float grad_scale,
+                  void* stream);
+
+/* -------------------------------------------------------------------------------- file reader
+ * Host-side CDF-5 ("64BIT_DATA") reader: the subset of PnetCDF the path uses
+ * (pncpy.File(path,'r') mp:31, variables[...].shape mp:37, per-sample gets mp:43/46 — served here
+ * as row-range reads so a rank can pull a contiguous slab straight into pinned memory). */
+typedef struct ddpm_cdf5 ddpm_cdf5;
+int  ddpm_cdf5_open(const char* path, ddpm_cdf5** out);
+void ddpm_cdf5_close(ddpm_cdf5* f);
+/* ndims <= 8; dims[] receives the shape; *elem_size the element size in bytes; *begin the
+ * variable's file offset. Returns non-zero if the variable does not exist. */
+int  ddpm_cdf5_inq_var(const ddpm_cdf5* f, const char* name, int* ndims, int64_t* dims,
+                       int* nc_type, int* elem_size, int64_t* begin);
+/* Reads rows [row0, row0+nrows) of a variable (row = index along the first dimension) into
+ * h_dst with positioned reads; thread-safe for concurrent calls on one handle. */
+int  ddpm_cdf5_read_rows(const ddpm_cdf5* f, const char* name, int64_t row0, int64_t nrows,
+                         void* h_dst);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDPMNIST_B200_H */

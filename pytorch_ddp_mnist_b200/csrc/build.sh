@@ -1,0 +1,11 @@
+#!/bin/bash
+# Builds libddpmnist_b200.so in-tree for sm_100a (cross-compiles without a GPU).
+set -euo pipefail
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+OUT="${HERE}/../libddpmnist_b200.so"
+NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
+"${NVCC}" -shared -Xcompiler -fPIC -O3 -std=c++17 -lineinfo \
+    -gencode arch=compute_100a,code=sm_100a \
+    ${DDPM_PTXAS_V:+-Xptxas -v} \
+    -o "${OUT}" "${HERE}/mnist_kernels.cu" "${HERE}/cdf5_reader.cpp" ${DDPM_EXTRA_SRC:-} -lcudart
+echo "built ${OUT}"

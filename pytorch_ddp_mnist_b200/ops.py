@@ -1,0 +1,156 @@
+"""Tensor-level wrappers over the C ABI: argument checks + pointer plumbing, nothing else.
+
+Every function launches on torch's current CUDA stream and returns without synchronising.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import CLASSES, HID, IN, N_PARAMS, check, cur_stream, lib, ptr
+
+__all__ = ["decode_lut", "gather_decode", "dropout_mask_philox", "Workspace", "step_forward",
+           "step_backward", "cross_entropy", "sgd_step"]
+
+
+def _need(t: Optional[torch.Tensor], name: str, dtype, shape=None, optional=False):
+    if t is None:
+        if optional:
+            return
+        raise ValueError(f"{name} is required")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (this library has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError(f"{name} must have shape {tuple(shape)}, got {tuple(t.shape)}")
+
+
+def decode_lut() -> torch.Tensor:
+    """256-entry fp32 decode table, computed by the library on the host."""
+    out = torch.empty(256, dtype=torch.float32)
+    check(lib.ddpm_decode_lut_host(out.data_ptr()))
+    return out
+
+
+def gather_decode(images: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor,
+                  out_x: Optional[torch.Tensor] = None, out_y: Optional[torch.Tensor] = None,
+                  status: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(x f32[B,784], y u8[B]) for sample indices idx i64[B] of the resident u8 dataset."""
+    n = images.shape[0]
+    _need(images, "images", torch.uint8)
+    if images.numel() != n * IN:
+        raise ValueError("images must hold 784 bytes per sample")
+    _need(labels, "labels", torch.uint8, (n,))
+    _need(idx, "idx", torch.int64)
+    b = idx.numel()
+    if out_x is None:
+        out_x = torch.empty((b, IN), dtype=torch.float32, device=images.device)
+    if out_y is None:
+        out_y = torch.empty((b,), dtype=torch.uint8, device=images.device)
+    _need(out_x, "out_x", torch.float32, (b, IN))
+    _need(out_y, "out_y", torch.uint8, (b,))
+    _need(status, "status", torch.int32, optional=True)
+    check(lib.ddpm_gather_decode(ptr(images), ptr(labels), n, ptr(idx), b, ptr(out_x), ptr(out_y),
+                                 ptr(status), cur_stream()))
+    return out_x, out_y
+
+
+def dropout_mask_philox(batch: int, seed: int, step: int, device, out: Optional[torch.Tensor] = None
+                        ) -> torch.Tensor:
+    if out is None:
+        out = torch.empty((batch, HID), dtype=torch.uint8, device=device)
+    _need(out, "out", torch.uint8, (batch, HID))
+    check(lib.ddpm_dropout_mask_philox(ptr(out), batch, seed, step, cur_stream()))
+    return out
+
+
+class Workspace:
+    """Caller-owned scratch for the fused step (see ddpm_workspace_bytes in the header)."""
+
+    def __init__(self, max_batch: int, device):
+        self.max_batch = int(max_batch)
+        nbytes = lib.ddpm_workspace_bytes(self.max_batch)
+        if nbytes == 0:
+            raise ValueError("max_batch must be positive")
+        # torch's caching allocator hands out >= 512-byte aligned blocks
+        self.buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        if self.buf.data_ptr() % 256:
+            raise RuntimeError("workspace is not 256-byte aligned")
+        check(lib.ddpm_workspace_init(ptr(self.buf), self.max_batch, cur_stream()))
+
+    @property
+    def nbytes(self) -> int:
+        return self.buf.numel()
+
+
+def step_forward(params: torch.Tensor, ws: Workspace, batch: int, *,
+                 images: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None,
+                 idx: Optional[torch.Tensor] = None, x: Optional[torch.Tensor] = None,
+                 y: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None,
+                 philox: Optional[Tuple[int, int]] = None, prep_backward: bool = False,
+                 logits: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None) -> None:
+    _need(params, "params", torch.float32, (N_PARAMS,))
+    if batch > ws.max_batch:
+        raise ValueError(f"batch {batch} exceeds workspace max_batch {ws.max_batch}")
+    n = 0
+    if x is not None:
+        _need(x, "x", torch.float32, (batch, IN))
+    else:
+        _need(images, "images", torch.uint8)
+        _need(idx, "idx", torch.int64)
+        if idx.numel() < batch:
+            raise ValueError("idx shorter than batch")
+        n = images.shape[0]
+        _need(labels, "labels", torch.uint8, (n,), optional=True)
+    _need(y, "y", torch.uint8, optional=True)
+    _need(mask, "mask", torch.uint8, (batch, HID), optional=True)
+    _need(logits, "logits", torch.float32, (batch, CLASSES), optional=True)
+    _need(loss, "loss", torch.float32, (2,), optional=True)
+    flags = (_lib.FWD_PREP_BACKWARD if prep_backward else 0) | (_lib.FWD_PHILOX_MASK if philox else 0)
+    seed, step = philox if philox else (0, 0)
+    check(lib.ddpm_step_forward(ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(x), ptr(y),
+                                ptr(mask), seed, step, batch, flags, ptr(logits), ptr(loss),
+                                ptr(ws.buf), cur_stream()))
+
+
+def step_backward(params: torch.Tensor, ws: Workspace, batch: int, *,
+                  images: Optional[torch.Tensor] = None, idx: Optional[torch.Tensor] = None,
+                  x: Optional[torch.Tensor] = None, dlogits: Optional[torch.Tensor] = None,
+                  grads: Optional[torch.Tensor] = None, grad_scale: float = 1.0, lr: float = 0.0) -> None:
+    _need(params, "params", torch.float32, (N_PARAMS,))
+    _need(grads, "grads", torch.float32, (N_PARAMS,), optional=True)
+    _need(dlogits, "dlogits", torch.float32, (batch, CLASSES), optional=True)
+    n = 0
+    if x is not None:
+        _need(x, "x", torch.float32, (batch, IN))
+    else:
+        _need(images, "images", torch.uint8)
+        _need(idx, "idx", torch.int64)
+        n = images.shape[0]
+    check(lib.ddpm_step_backward(ptr(params), ptr(images), n, ptr(idx), ptr(x), ptr(dlogits), batch,
+                                 grad_scale, lr, ptr(grads), ptr(ws.buf), cur_stream()))
+
+
+def cross_entropy(logits: torch.Tensor, y: torch.Tensor, loss: Optional[torch.Tensor] = None,
+                  dlogits: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    _need(logits, "logits", torch.float32)
+    b = logits.shape[0]
+    if tuple(logits.shape) != (b, CLASSES):
+        raise ValueError("logits must be [B,10]")
+    _need(y, "y", torch.uint8, (b,))
+    if loss is None:
+        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+    _need(dlogits, "dlogits", torch.float32, (b, CLASSES), optional=True)
+    check(lib.ddpm_cross_entropy(ptr(logits), ptr(y), b, ptr(loss), ptr(dlogits), cur_stream()))
+    return loss, dlogits
+
+
+def sgd_step(params: torch.Tensor, grads: torch.Tensor, lr: float, grad_scale: float = 1.0) -> None:
+    _need(params, "params", torch.float32)
+    _need(grads, "grads", torch.float32, tuple(params.shape))
+    check(lib.ddpm_sgd_step(ptr(params), ptr(grads), params.numel(), lr, grad_scale, cur_stream()))

@@ -1,0 +1,304 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the reference-generated
+golden fixtures.  Needs a B200; run with `pytest -m gpu`."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+pytestmark = pytest.mark.gpu
+
+from oracle import mnist_oracle as O  # noqa: E402  (checker only)
+
+TOL_F32 = 2e-5      # fp32 FFMA kernels vs fp32 oracle / ATen: summation order only (<=1e-5..)
+TOL_TRAJ = 5e-3     # 100 free-running steps (ReLU gate flips, see tests/test_oracle.py)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from pytorch_ddp_mnist_b200 import ops as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def data(dev, synth_train):
+    im, lb = synth_train
+    return (torch.from_numpy(im.reshape(-1, 784)).to(dev), torch.from_numpy(lb).to(dev), im, lb)
+
+
+def _rel(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def _fro(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def _params(g, prefix):
+    return {k: g[f"{prefix}.{k}"] for k in O.PARAM_KEYS}
+
+
+def _flat(p, dev):
+    return torch.from_numpy(O.flatten_params(p)).to(dev)
+
+
+# ------------------------------------------------------------------------------ K1
+def test_decode_lut_host_bit_exact(ops):
+    assert np.array_equal(ops.decode_lut().numpy().view(np.uint32), O.decode_lut().view(np.uint32))
+
+
+@pytest.mark.parametrize("batch", [1, 7, 12, 64, 100, 4096])
+def test_gather_decode_bit_exact(ops, dev, data, batch):
+    images, labels, im, lb = data
+    rng = np.random.default_rng(batch)
+    idx = rng.integers(0, im.shape[0], batch).astype(np.int64)
+    idx[0] = 0
+    idx[-1] = im.shape[0] - 1
+    x, y = ops.gather_decode(images, labels, torch.from_numpy(idx).to(dev))
+    xr, yr = O.gather_decode(im, lb, idx)
+    assert np.array_equal(x.cpu().numpy().view(np.uint32), xr.view(np.uint32))
+    assert np.array_equal(y.cpu().numpy(), yr)
+
+
+def test_gather_decode_golden_step0(ops, dev, data, golden):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    x, y = ops.gather_decode(images, labels, torch.from_numpy(g["idx"][0]).to(dev))
+    assert np.array_equal(x.cpu().numpy().view(np.uint32), g["x0"].view(np.uint32))
+    assert np.array_equal(y.cpu().numpy(), g["y0"])
+
+
+def test_gather_decode_edges(ops, dev, data):
+    images, labels, im, _ = data
+    # empty batch is a no-op
+    x, y = ops.gather_decode(images, labels, torch.empty(0, dtype=torch.int64, device=dev))
+    assert x.shape == (0, 784) and y.shape == (0,)
+    # out-of-range index: flagged on the device, row poisoned, neighbours intact
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    idx = torch.tensor([3, im.shape[0], -1, 5], dtype=torch.int64, device=dev)
+    x, y = ops.gather_decode(images, labels, idx, status=status)
+    assert int(status.item()) == 1
+    xn = x.cpu().numpy()
+    assert np.isnan(xn[1]).all() and np.isnan(xn[2]).all()
+    assert np.array_equal(xn[0].view(np.uint32), O.decode_lut()[im[3].reshape(-1)].view(np.uint32))
+    with pytest.raises(TypeError):
+        ops.gather_decode(images, labels, idx.to(torch.int32))
+    with pytest.raises(ValueError):
+        ops.gather_decode(images.cpu(), labels, idx)
+
+
+# ------------------------------------------------------------------------------ step 0 vs reference
+@pytest.mark.parametrize("src", ["u8", "f32"])
+def test_step0_against_reference(ops, dev, data, golden, src):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    idx = torch.from_numpy(g["idx"][0]).to(dev)
+    p0 = _params(g, "params0")
+    params = _flat(p0, dev)
+    mask = torch.from_numpy(O.unpack_masks(g["masks"])[0]).to(dev)
+    ws = ops.Workspace(64, dev)
+    logits = torch.empty(64, 10, device=dev)
+    loss = torch.zeros(2, device=dev)
+    grads = torch.zeros(O.N_PARAMS, device=dev)
+    kw = dict(images=images, labels=labels, idx=idx) if src == "u8" else \
+        dict(x=torch.from_numpy(g["x0"]).to(dev), y=torch.from_numpy(g["y0"]).to(dev))
+    ops.step_forward(params, ws, 64, mask=mask, prep_backward=True, logits=logits, loss=loss, **kw)
+    bkw = dict(images=images, idx=idx) if src == "u8" else dict(x=kw["x"])
+    ops.step_backward(params, ws, 64, grads=grads, **bkw)
+    torch.cuda.synchronize()
+    assert _rel(logits.cpu().numpy(), g["acts0.5"]) < TOL_F32
+    assert abs(float(loss[0]) - float(g["losses"][0])) < 1e-5
+    assert abs(float(loss[1]) - float(g["losses"][0]) / 64) < 1e-6      # mp:465 bookkeeping
+    gflat = grads.cpu().numpy()
+    gu = O.unflatten_params(gflat)
+    for k in O.PARAM_KEYS:
+        assert _rel(gu[k], g[f"grads0.{k}"]) < TOL_F32, k
+    # params untouched when lr == 0
+    assert torch.equal(params, _flat(p0, dev))
+    # fused SGD epilogue == separate SGD kernel == reference params after one step
+    p_fused = params.clone()
+    ops.step_forward(p_fused, ws, 64, mask=mask, prep_backward=True, **kw)
+    ops.step_backward(p_fused, ws, 64, lr=0.01, **bkw)
+    p_sep = params.clone()
+    ops.sgd_step(p_sep, grads, 0.01)
+    torch.cuda.synchronize()
+    assert torch.equal(p_fused, p_sep)
+    pu = O.unflatten_params(p_sep.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _rel(pu[k], g[f"params1.{k}"]) < 1e-6, k
+
+
+def test_sgd_bit_exact_with_reference(ops, dev, golden):
+    g = golden["traj_ws1"]
+    p = _flat(_params(g, "params0"), dev)
+    gr = _flat(_params(g, "grads0"), dev)
+    ops.sgd_step(p, gr, 0.01)
+    want = O.flatten_params(_params(g, "params1"))
+    assert np.array_equal(p.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    # odd length exercises the scalar tail; grad_scale folds DDP's 1/ws
+    q = torch.arange(1003, dtype=torch.float32, device=dev) / 7
+    h = torch.ones(1003, device=dev)
+    ops.sgd_step(q, h, 0.5, 0.25)
+    assert torch.allclose(q, torch.arange(1003, dtype=torch.float32, device=dev) / 7 - 0.125)
+
+
+def test_external_dlogits_path_matches_internal(ops, dev, data, golden):
+    """autograd route: forward -> ddpm_cross_entropy -> backward(dlogits) gives the same gradients
+    as the fused route, bit for bit (same code, same order)."""
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    idx = torch.from_numpy(g["idx"][1]).to(dev)
+    params = _flat(_params(g, "params1"), dev)
+    mask = torch.from_numpy(O.unpack_masks(g["masks"])[1]).to(dev)
+    ws = ops.Workspace(64, dev)
+    loss = torch.zeros(2, device=dev)
+    g1 = torch.zeros(O.N_PARAMS, device=dev)
+    ops.step_forward(params, ws, 64, images=images, labels=labels, idx=idx, mask=mask,
+                     prep_backward=True, loss=loss)
+    ops.step_backward(params, ws, 64, images=images, idx=idx, grads=g1)
+    logits = torch.empty(64, 10, device=dev)
+    _, y = ops.gather_decode(images, labels, idx)
+    ops.step_forward(params, ws, 64, images=images, idx=idx, mask=mask, prep_backward=True, logits=logits)
+    dl = torch.empty(64, 10, device=dev)
+    l2, _ = ops.cross_entropy(logits, y, dlogits=dl)
+    g2 = torch.zeros(O.N_PARAMS, device=dev)
+    ops.step_backward(params, ws, 64, images=images, idx=idx, dlogits=dl, grads=g2)
+    torch.cuda.synchronize()
+    assert abs(float(l2) - float(loss[0])) < 1e-6
+    assert abs(float(l2) - float(g["losses"][1])) < 1e-5
+    assert torch.equal(g1, g2)
+
+
+# ------------------------------------------------------------------------------ shapes / edges
+@pytest.mark.parametrize("batch", [1, 12, 33, 148, 149, 592, 600, 1024, 4096])
+def test_step_matches_oracle_all_batch_sizes(ops, dev, data, golden, batch):
+    g = golden["traj_ws1"]
+    images, labels, im, lb = data
+    rng = np.random.default_rng(1000 + batch)
+    idx_np = rng.integers(0, 60000, batch).astype(np.int64)
+    mask_np = (rng.random((batch, 128)) < 0.8).astype(np.uint8)
+    p = _params(g, "paramsN")                      # trained weights: non-trivial activations
+    x, y = O.gather_decode(im, lb, idx_np)
+    a = O.forward(p, x, mask_np)
+    loss_ref, dz3 = O.cross_entropy(a["z3"], y)
+    gr = O.backward(p, x, a, mask_np, dz3)
+
+    params = _flat(p, dev)
+    ws = ops.Workspace(batch, dev)
+    logits = torch.empty(batch, 10, device=dev)
+    loss = torch.zeros(2, device=dev)
+    grads = torch.zeros(O.N_PARAMS, device=dev)
+    idx = torch.from_numpy(idx_np).to(dev)
+    ops.step_forward(params, ws, batch, images=images, labels=labels, idx=idx,
+                     mask=torch.from_numpy(mask_np).to(dev), prep_backward=True, logits=logits, loss=loss)
+    ops.step_backward(params, ws, batch, images=images, idx=idx, grads=grads, grad_scale=0.5)
+    torch.cuda.synchronize()
+    assert _rel(logits.cpu().numpy(), a["z3"]) < TOL_F32
+    assert abs(float(loss[0]) - float(loss_ref)) < 2e-5 * max(1.0, abs(float(loss_ref)))
+    gu = O.unflatten_params(grads.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _rel(gu[k], 0.5 * gr[k]) < 5e-5, k           # 0.5 = DDP pre-division for ws=2
+
+
+def test_eval_forward(ops, dev, data, golden, synth_test):
+    g = golden["traj_ws1"]
+    p = _params(g, "paramsN")
+    im, lb = synth_test
+    images = torch.from_numpy(im.reshape(-1, 784)).to(dev)
+    labels = torch.from_numpy(lb).to(dev)
+    idx_np = np.arange(300, 300 + 80, dtype=np.int64)
+    x, y = O.gather_decode(im, lb, idx_np)
+    ref = O.eval_loss(p, x, y)
+    params = _flat(p, dev)
+    ws = ops.Workspace(80, dev)
+    loss = torch.zeros(2, device=dev)
+    ops.step_forward(params, ws, 80, images=images, labels=labels, idx=torch.from_numpy(idx_np).to(dev), loss=loss)
+    ops.step_forward(params, ws, 80, images=images, labels=labels, idx=torch.from_numpy(idx_np).to(dev), loss=loss)
+    torch.cuda.synchronize()
+    assert abs(float(loss[0]) - float(ref)) < 2e-5
+    assert abs(float(loss[1]) - 2 * float(ref) / 80) < 1e-6     # accumulates across calls (mp:481)
+
+
+def test_argument_errors(ops, dev, data):
+    images, labels, _, _ = data
+    ws = ops.Workspace(8, dev)
+    params = torch.zeros(O.N_PARAMS, device=dev)
+    idx = torch.zeros(8, dtype=torch.int64, device=dev)
+    with pytest.raises(ValueError, match="exceeds workspace"):
+        ops.step_forward(params, ws, 9, images=images, labels=labels, idx=idx)
+    from pytorch_ddp_mnist_b200._lib import DDPMError
+    with pytest.raises(DDPMError, match="nothing to do"):
+        ops.step_backward(params, ws, 8, images=images, idx=idx)
+    with pytest.raises(DDPMError, match="batch must be positive"):
+        ops.step_forward(params, ws, 0, images=images, labels=labels, idx=idx)
+
+
+# ------------------------------------------------------------------------------ dropout (perf mode)
+def test_philox_mask(ops, dev, data, golden):
+    m1 = ops.dropout_mask_philox(4096, seed=42, step=3, device=dev)
+    m2 = ops.dropout_mask_philox(4096, seed=42, step=3, device=dev)
+    m3 = ops.dropout_mask_philox(4096, seed=42, step=4, device=dev)
+    assert torch.equal(m1, m2) and not torch.equal(m1, m3)
+    keep = m1.float().mean().item()
+    assert abs(keep - 0.8) < 4 * (0.8 * 0.2 / m1.numel()) ** 0.5            # 4 sigma
+    assert set(np.unique(m1.cpu().numpy()).tolist()) == {0, 1}
+    # the in-kernel mask of the fused step is the same stream
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    params = _flat(_params(g, "params0"), dev)
+    idx = torch.from_numpy(g["idx"][0]).to(dev)
+    ws = ops.Workspace(64, dev)
+    la, lb_ = torch.empty(64, 10, device=dev), torch.empty(64, 10, device=dev)
+    ops.step_forward(params, ws, 64, images=images, labels=labels, idx=idx, philox=(42, 3), logits=la)
+    ops.step_forward(params, ws, 64, images=images, labels=labels, idx=idx, mask=m1[:64].contiguous(), logits=lb_)
+    torch.cuda.synchronize()
+    assert torch.equal(la, lb_)
+
+
+# ------------------------------------------------------------------------------ trajectory
+def test_trajectory_100_steps_vs_reference(ops, dev, data, golden):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    params = _flat(_params(g, "params0"), dev)
+    masks = torch.from_numpy(O.unpack_masks(g["masks"])).to(dev)
+    idx_all = torch.from_numpy(g["idx"]).to(dev)
+    ws = ops.Workspace(64, dev)
+    loss = torch.zeros(2, device=dev)
+    losses = torch.zeros(100, device=dev)
+    for t in range(100):
+        ops.step_forward(params, ws, 64, images=images, labels=labels, idx=idx_all[t], mask=masks[t],
+                         prep_backward=True, loss=loss)
+        ops.step_backward(params, ws, 64, images=images, idx=idx_all[t], lr=0.01)
+        losses[t] = loss[0]
+    torch.cuda.synchronize()
+    ln = losses.cpu().numpy()
+    assert np.abs(ln[:5] - g["losses"][:5]).max() < 1e-5
+    assert np.abs(ln - g["losses"]).max() < TOL_TRAJ * np.abs(g["losses"]).max()
+    pu = O.unflatten_params(params.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _fro(pu[k], g[f"paramsN.{k}"]) < TOL_TRAJ, k
+    # epoch bookkeeping accumulated on the device == sum(loss_b / B_b)
+    assert abs(float(loss[1]) - float(ln.astype(np.float64).sum() / 64)) < 1e-4
+
+
+def test_run_to_run_determinism(ops, dev, data, golden):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    outs = []
+    for _ in range(2):
+        params = _flat(_params(g, "params0"), dev)
+        ws = ops.Workspace(64, dev)
+        for t in range(10):
+            idx = torch.from_numpy(g["idx"][t]).to(dev)
+            ops.step_forward(params, ws, 64, images=images, labels=labels, idx=idx, philox=(7, t), prep_backward=True)
+            ops.step_backward(params, ws, 64, images=images, idx=idx, lr=0.01)
+        outs.append(params.clone())
+    assert torch.equal(outs[0], outs[1])
