@@ -300,7 +300,9 @@ rows_kernel(RowsArgs a) {
     const bool bwd_only = (a.flags & ROWS_BWD_ONLY) != 0;
     const bool prep_bwd = bwd_only || (a.flags & DDPM_FWD_PREP_BACKWARD);
     const bool philox = (a.flags & DDPM_FWD_PHILOX_MASK) != 0;
-    const bool train = philox || a.mask != nullptr;
+    // the backward half must use the dropout scale of the forward that filled the workspace
+    const bool train = bwd_only ? (__ldcg(a.ctrl + 1) != 0u) : (philox || a.mask != nullptr);
+    if (!bwd_only && blockIdx.x == 0 && j == 0) a.ctrl[1] = train ? 1u : 0u;
     const bool have_y = a.y != nullptr || (a.labels != nullptr && a.idx != nullptr);
     const float scale = train ? 1.25f : 1.0f;       // 1/(1-0.2), exact
     const int B = a.B;
