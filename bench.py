@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: one data-parallel MNIST training step (reference model `ref_mlp`,
+`mnist_pnetcdf_cpu_mp.py:453-466`) on synthetic MNIST-shaped data.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 64] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Prints ONE JSON line on rank 0.  See DESIGN.md §6 for what every field means.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+if REPO not in sys.path:
+    sys.path.insert(0, REPO)
+
+METRIC = "MNIST-ConvNet train images/sec at 1/2/4/8 B200 + % roofline vs CPU gloo ref"   # BASELINE.json
+UNIT = "images/s"
+BENCH_N = 240_000          # 188 MB of u8 pixels: larger than the 126 MB L2
+BENCH_SEED = 1234
+CHUNK = 100                # steps unrolled per CUDA graph
+
+
+def _peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period_s
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.err = None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+                nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+            }
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(self.period)
+        except Exception as e:                                   # NVML missing: report it
+            self.err = repr(e)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s), **({"error": self.err} if self.err else {})}
+
+
+# ------------------------------------------------------------------------------------ reference arm
+def run_reference_arm(args) -> None:
+    """`--impl reference`: the reference's own CPU path (gloo DDP, world_size 2, per-sample netCDF
+    loader) on the host cores, via oracle/ref_port.py (the Python reference cannot travel to the
+    GPU box; the port is checked against it in tests/test_ref_port.py)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref_port
+    from pytorch_ddp_mnist_b200 import synth
+    steps = max(1, min(args.steps, 400))            # bounded sample: ~10 ms/step on CPU
+    warmup = max(1, min(args.warmup, 20))
+    with tempfile.TemporaryDirectory() as d:
+        synth.write_default_files(d, 60_000, 1_000)
+        r = ref_port.time_port_gloo(d, args.batch, steps, warmup, world_size=2, port=29700 + os.getpid() % 200)
+    v = r["images_per_s"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * r["seconds"] / steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": _config(args, extra={"reference_world_size": 2}),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": f"{steps} steps x batch {args.batch} x 2 gloo ranks "
+                                   f"({r['threads_per_rank']} threads each) of epoch 0, synthetic 60000-sample CDF-5 file; "
+                                   f"loader share {r['loader_fraction']:.2f}"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def _config(args, extra=None):
+    c = {"workload": f"ref_mlp (784-128-128-10 MLP, the model the reference actually defines) training step, "
+                     f"batch {args.batch}/rank, CrossEntropy + SGD(lr=0.01), dropout 0.2; BASELINE.json configs[1] "
+                     f"(the 'ConvNet' it names does not exist in the reference, SURVEY.md §0)",
+         "batch_per_rank": args.batch, "dataset_samples": BENCH_N,
+         "l2": "resident u8 dataset is 188 MB (> 126 MB L2) and every step gathers rows not touched before; "
+               "weights stay L2-resident as in any training loop",
+         "graph_chunk_steps": CHUNK}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ------------------------------------------------------------------------------------ our arm
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-baseline-steps", type=int, default=150)
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from pytorch_ddp_mnist_b200 import engine as E, ops, synth
+    from pytorch_ddp_mnist_b200.dataset import ResidentDataset
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", init_method="env://", device_id=dev)
+    B, K, W = args.batch, args.steps, args.warmup
+
+    # ---- data: resident u8 dataset (same bytes on every rank), epoch-0 shard of this rank
+    im, lb = synth.synth(BENCH_N, BENCH_SEED)
+    resident = ResidentDataset.from_arrays(im, lb, dev)
+    from torch.utils.data import DistributedSampler
+    from pytorch_ddp_mnist_b200.dataset import _IndexOnly
+    sampler = DistributedSampler(_IndexOnly(BENCH_N), num_replicas=world, rank=rank, shuffle=True, seed=42)
+    sampler.set_epoch(0)
+    shard = torch.tensor(list(iter(sampler)), dtype=torch.int64)
+    need = (W + K + CHUNK) * B
+    reps = -(-need // shard.numel())
+    shard_dev = shard.repeat(reps)[:need].to(dev)          # wraps after 3750/ws steps; rows long evicted by then
+
+    torch.manual_seed(0)
+    eng = E.TrainEngine(dev, B, lr=0.01, world_size=world, rank=rank)
+    eng.load_state_dict(E.init_params_like_reference())
+    eng.broadcast_params()
+
+    # ---- graph of CHUNK unrolled steps reading a fixed index buffer that is refilled per replay
+    chunk = min(CHUNK, K)
+    idx_buf = torch.empty(chunk * B, dtype=torch.int64, device=dev)
+    idx_buf.copy_(shard_dev[:chunk * B])
+    batches = list(torch.split(idx_buf, B))
+    for t in range(3):                                      # eager warm-up (also warms NCCL)
+        eng.train_step(resident, batches[t % chunk])
+    graph = eng.capture_steps(resident, batches)
+    kernels_per_step = 3 if world == 1 else 4               # fc1_fwd, rows, grads (+ sgd); NCCL's kernel not counted
+
+    def run(n_steps: int, start_step: int) -> int:
+        """n_steps optimisation steps starting at global step `start_step`; returns launches."""
+        done, launches = 0, 0
+        while done + chunk <= n_steps:
+            s = (start_step + done) * B
+            idx_buf.copy_(shard_dev[s:s + chunk * B])
+            graph.replay()
+            done += chunk
+            launches += chunk * kernels_per_step
+        while done < n_steps:                               # remainder, eager
+            s = (start_step + done) * B
+            eng.train_step(resident, shard_dev[s:s + B])
+            done += 1
+            launches += kernels_per_step
+        return launches
+
+    run(W, 0)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler_thr = ClockSampler(local_rank)
+    sampler_thr.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    launches = run(K, W)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler_thr.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = K * B * world / (ms * 1e-3)
+    final_loss = eng.last_batch_loss()
+
+    # ---- per-kernel durations, live, with CUDA events on the launching stream
+    kern = _time_kernels(torch, ops, eng, resident, shard_dev, B, world)
+
+    # ---- e2e: host buffers in, loss out, every step
+    e2e = _time_e2e(torch, eng, im, lb, shard, B, min(K, 2000), world, dev, dist if world > 1 else None)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": _config(args, {"final_batch_loss": final_loss}),
+        "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": kern["roofline"],
+        "kernels": kern["kernels"],
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = _cpu_baseline(args)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _time_kernels(torch, ops, eng, resident, shard_dev, B, world):
+    """Average duration of each of the step's kernels, measured with CUDA events around runs of
+    that kernel alone on fresh (cold) rows, and the HBM roofline of the dominant one.
+    Algorithmic bytes per launch: pixels 784 B + index 8 B (+ label 1 B) per image,
+    each parameter/activation tensor the phase must read or write once."""
+    hbm, which = _peaks()
+    P = 473_088
+    reps = 200
+    lr = eng.lr if world == 1 else 0.0
+    gscale = 1.0 / world
+    grads = eng.grads if world > 1 else None
+    params = eng.params.clone()                              # do not disturb the trained weights
+    idxs = [shard_dev[i * B:(i + 1) * B] for i in range(reps)]
+    mask_kw = dict(philox=(1, 0))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+    def avg_ms(fn):
+        for i in range(5):
+            fn(idxs[i])
+        torch.cuda.synchronize()
+        ev[0].record()
+        for i in range(reps):
+            fn(idxs[i])
+        ev[1].record()
+        torch.cuda.synchronize()
+        return ev[0].elapsed_time(ev[1]) / reps
+
+    # forward = fc1_fwd + rows; backward = grads (+sgd when ws>1).  Separate them by difference.
+    def fwd(idx):
+        ops.step_forward(params, eng.ws, B, images=resident.images, labels=resident.labels, idx=idx,
+                         prep_backward=True, loss=eng.loss, **mask_kw)
+
+    def bwd(idx):
+        ops.step_backward(params, eng.ws, B, images=resident.images, idx=idx, grads=grads, grad_scale=gscale, lr=lr)
+
+    def gather_only(idx):
+        ops.gather_decode(resident.images, resident.labels, idx, out_x=xbuf, out_y=ybuf)
+
+    xbuf = torch.empty(B, 784, device=params.device)
+    ybuf = torch.empty(B, dtype=torch.uint8, device=params.device)
+    t_fwd, t_bwd, t_gather = avg_ms(fwd), avg_ms(bwd), avg_ms(gather_only)
+    bytes_fwd = B * (784 + 8 + 1) + (100_352 + 128) * 4 + 71_680 + 4 * B * 512 + B * 64   # px,idx,label + W1,b1 + W2,b2,W3 + h1d,h2,dz2,dz1 + dz3
+    bytes_bwd = B * (784 + 8) + 4 * B * 512 + B * 64 + 2 * P + (P if world > 1 else 0)    # px again + activations + params r/w (+ bucket)
+    bytes_gather = B * (784 + 8 + 1) + B * (3136 + 1)
+    kernels = [
+        {"name": "step_forward (fc1_fwd_kernel + rows_kernel)", "ms": t_fwd, "alg_bytes": bytes_fwd,
+         "gbs": bytes_fwd / t_fwd / 1e6},
+        {"name": "step_backward (grads_kernel, SGD fused)" if world == 1 else "step_backward (grads_kernel -> bucket)",
+         "ms": t_bwd, "alg_bytes": bytes_bwd, "gbs": bytes_bwd / t_bwd / 1e6},
+        {"name": "gather_decode_kernel (standalone loader kernel, not in the fused step)", "ms": t_gather,
+         "alg_bytes": bytes_gather, "gbs": bytes_gather / t_gather / 1e6},
+    ]
+    dom = max(kernels[:2], key=lambda k: k["ms"])
+    roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": hbm, "unit": "GB/s", "frac": dom["gbs"] / hbm,
+            "traffic": None, "kernel": dom["name"], "peak_source": which,
+            "note": "host-launched back to back (includes launch gaps); batch-64 steps are launch/latency-bound, "
+                    "see DESIGN.md §4"}
+    return {"kernels": kernels, "roofline": roof}
+
+
+def _time_e2e(torch, eng, im, lb, shard, B, steps, world, dev, dist):
+    """Same metric through the public step API with HOST inputs: per step, H2D of the batch's u8
+    pixels + labels from pinned memory, the fused step, and a D2H read of the loss."""
+    import numpy as np
+    steps = max(steps, 10)
+    rows = shard[: (steps + 10) * B].numpy() % im.shape[0]
+    host_x = torch.from_numpy(im.reshape(-1, 784)[rows]).pin_memory()
+    host_y = torch.from_numpy(lb[rows]).pin_memory()
+    x_dev = [torch.empty(B, 784, dtype=torch.uint8, device=dev) for _ in range(2)]
+    y_dev = [torch.empty(B, dtype=torch.uint8, device=dev) for _ in range(2)]
+    ident = torch.arange(B, dtype=torch.int64, device=dev)
+    loss_host = torch.zeros(steps + 10, 2).pin_memory()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def one(t, sync):
+        b = t & 1
+        x_dev[b].copy_(host_x[t * B:(t + 1) * B], non_blocking=True)
+        y_dev[b].copy_(host_y[t * B:(t + 1) * B], non_blocking=True)
+        eng.train_step_host_batch(x_dev[b], y_dev[b], ident)
+        loss_host[t].copy_(eng.loss, non_blocking=True)
+        if sync:
+            torch.cuda.current_stream().synchronize()       # the reference's per-step .item() (mp:464)
+
+    out = {}
+    for name, sync in (("pipelined", False), ("sync_each_step", True)):
+        for t in range(10):
+            one(t, sync)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ev0.record()
+        for t in range(10, 10 + steps):
+            one(t, sync)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        if dist is not None:
+            tt = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        out[name] = steps * B * world / (ms * 1e-3)
+    assert bool(torch.isfinite(loss_host[10:10 + steps, 0]).all())
+    return {"value": out["pipelined"], "unit": UNIT, "h2d_bytes_per_step": B * 785, "d2h_bytes_per_step": 8,
+            "steps": steps, "sync_each_step_value": out["sync_each_step"],
+            "note": "value: loss copied D2H asynchronously every step, one sync at the end; sync_each_step_value: "
+                    "host waits for every step's loss like the reference's batch_loss.item()"}
+
+
+def _cpu_baseline(args):
+    """The reference's CPU path (port, checked against the reference in tests/test_ref_port.py),
+    2 gloo ranks on this box's cores, bounded sample."""
+    code = ("import json,sys,tempfile;sys.path.insert(0,%r);"
+            "from oracle import ref_port;from pytorch_ddp_mnist_b200 import synth;"
+            "d=tempfile.mkdtemp();synth.write_default_files(d,60000,1000);"
+            "print('CPUBASE'+json.dumps(ref_port.time_port_gloo(d,%d,%d,10,2,29890)))") % (
+                REPO, args.batch, args.cpu_baseline_steps)
+    try:
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+        r = json.loads([l for l in out.stdout.splitlines() if l.startswith("CPUBASE")][-1][7:])
+        return {"value": r["images_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                "sample": f"{args.cpu_baseline_steps} steps x batch {args.batch} x 2 gloo ranks ({r['threads_per_rank']} "
+                          f"threads each), per-sample CDF-5 reads, loader share {r['loader_fraction']:.2f}, "
+                          f"{r['seconds']:.1f} s"}
+    except Exception as e:                                       # never lose the GPU line over the baseline
+        return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e!r}"}
+
+
+if __name__ == "__main__":
+    main()

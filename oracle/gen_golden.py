@@ -44,8 +44,6 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_DIR = "/root/reference"
-MASK_SEED0 = 10_000
-MODEL_SEED = 0
 
 
 def _setup_path():
@@ -62,29 +60,7 @@ from torch import nn  # noqa: E402
 from pytorch_ddp_mnist_b200 import synth  # noqa: E402
 
 
-# ----------------------------------------------------------------------------- determinisation
-class MaskFeed:
-    """Replaces nn.Dropout.forward; step counter advances once per training forward."""
-    def __init__(self):
-        self.step = 0
-        self.masks = []
-
-    def install(self):
-        feed = self
-
-        def forward(mod, x):
-            if not mod.training:
-                return x
-            g = torch.Generator().manual_seed(MASK_SEED0 + feed.step)
-            mask = torch.bernoulli(torch.full(x.shape, 1.0 - mod.p), generator=g)
-            feed.masks.append(mask.numpy().astype(np.uint8))
-            feed.step += 1
-            return x * (mask * (1.0 / (1.0 - mod.p)))
-        self._orig = nn.Dropout.forward
-        nn.Dropout.forward = forward
-
-    def remove(self):
-        nn.Dropout.forward = self._orig
+from oracle.determinism import MASK_SEED0, MODEL_SEED, MaskFeed  # noqa: E402,F401
 
 
 def _import_reference():

@@ -1,0 +1,159 @@
+"""The training-step engine: flat parameter bucket + fused CUDA step + (for ws > 1) one allreduce.
+
+Replaces the loop body `mp:455-465` of `mnist_pnetcdf_cpu_mp.py`:
+
+    x.view -> optimizer.zero_grad() -> model(x) -> loss(y_hat, y) -> backward() [DDP allreduce]
+    -> optimizer.step() -> epoch_loss += batch_loss.item() / B
+
+with, per step, on one stream:
+
+    ws == 1:  G1(fc1, decode fused) -> ROWS(fwd+loss+bwd chain) -> GRADS(+SGD fused)
+    ws  > 1:  G1 -> ROWS -> GRADS(bucket <- g/ws) -> allreduce(bucket, SUM) -> SGD(flat)
+
+Gradients live in ONE contiguous 473,088-byte bucket (the reference's DDP has exactly one bucket
+of that size), pre-divided by world_size as the c10d reducer does, so the collective is a plain SUM.
+The loss stays on the device: `loss[0]` is the batch mean, `loss[1]` accumulates the reference's
+`epoch_loss += batch_loss / B` bookkeeping; the host reads it once per epoch.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import ops
+from ._lib import N_PARAMS, OFF_B1, OFF_B2, OFF_W1, OFF_W2, OFF_W3
+
+PARAM_KEYS = ("0.weight", "0.bias", "3.weight", "3.bias", "5.weight")    # state_dict order, mp:412-422
+PARAM_SHAPES = ((128, 784), (128,), (128, 128), (128,), (10, 128))
+PARAM_OFFSETS = (OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3)
+
+
+def init_params_like_reference(generator: Optional[torch.Generator] = None) -> Dict[str, torch.Tensor]:
+    """nn.Linear's default init (kaiming_uniform(a=sqrt(5)) == U(-1/sqrt(in), 1/sqrt(in)) for both
+    weight and bias), drawn in `create_model()`'s order (mp:412-422) so that, with the same
+    torch.manual_seed, the values equal the reference's."""
+    from torch import nn
+    if generator is not None:
+        raise NotImplementedError("nn.Linear draws from the global generator; seed it with torch.manual_seed")
+    m = nn.Sequential(nn.Linear(28 * 28, 128), nn.ReLU(), nn.Dropout(0.2), nn.Linear(128, 128), nn.ReLU(),
+                      nn.Linear(128, 10, bias=False))
+    return {k: v.detach().clone() for k, v in m.state_dict().items()}
+
+
+class TrainEngine:
+    def __init__(self, device, max_batch: int, lr: float = 0.01, world_size: int = 1, rank: int = 0,
+                 group=None, seed: int = 42):
+        self.device = torch.device(device)
+        self.max_batch = int(max_batch)
+        self.lr = float(lr)
+        self.world_size, self.rank, self.group = int(world_size), int(rank), group
+        self.seed = int(seed) + 0x9E3779B97F4A7C15 * self.rank & 0xFFFFFFFFFFFFFFFF
+        self.params = torch.zeros(N_PARAMS, dtype=torch.float32, device=self.device)
+        self.grads = torch.zeros(N_PARAMS, dtype=torch.float32, device=self.device)   # the bucket
+        self.loss = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.ws = ops.Workspace(self.max_batch, self.device)
+        self.step_count = 0                       # Philox stream position (perf-mode dropout)
+
+    # ------------------------------------------------------------------ parameters
+    def views(self, flat: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        flat = self.params if flat is None else flat
+        out = {}
+        for k, shp, off in zip(PARAM_KEYS, PARAM_SHAPES, PARAM_OFFSETS):
+            n = 1
+            for s in shp:
+                n *= s
+            out[k] = flat[off:off + n].view(shp)
+        return out
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        v = self.views()
+        for k in PARAM_KEYS:
+            v[k].copy_(sd[k].to(torch.float32))
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """CPU tensors under the reference's keys (what `torch.save(model.state_dict())` holds, mp:511)."""
+        return {k: t.detach().cpu().clone() for k, t in self.views().items()}
+
+    def broadcast_params(self, src: int = 0) -> None:
+        """DDP construction semantics (mp:439): every rank adopts rank `src`'s parameters."""
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.broadcast(self.params, src=src, group=self.group)
+
+    # ------------------------------------------------------------------ steps
+    def train_step(self, resident, idx: torch.Tensor, mask: Optional[torch.Tensor] = None,
+                   philox_step: Optional[int] = None) -> None:
+        """Enqueue one optimisation step on the current stream for the samples `idx` (i64, device).
+        Dropout: `mask` u8[B,128] (parity mode) or the Philox stream at `philox_step`
+        (default: an internal counter)."""
+        b = idx.numel()
+        if mask is None:
+            st = self.step_count if philox_step is None else philox_step
+            kw = dict(philox=(self.seed, st))
+        else:
+            kw = dict(mask=mask)
+        self.step_count += 1
+        ops.step_forward(self.params, self.ws, b, images=resident.images, labels=resident.labels, idx=idx,
+                         prep_backward=True, loss=self.loss, **kw)
+        if self.world_size == 1:
+            ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, lr=self.lr)
+        else:
+            import torch.distributed as dist
+            ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
+                              grad_scale=1.0 / self.world_size)
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
+            ops.sgd_step(self.params, self.grads, self.lr)
+
+    def train_step_host_batch(self, x_u8: torch.Tensor, y_u8: torch.Tensor, idx_identity: torch.Tensor,
+                              mask: Optional[torch.Tensor] = None) -> None:
+        """Same step for a batch that was just copied from host memory (u8 [B,784] + u8 [B])."""
+        b = x_u8.shape[0]
+        kw = dict(mask=mask) if mask is not None else dict(philox=(self.seed, self.step_count))
+        self.step_count += 1
+        ops.step_forward(self.params, self.ws, b, images=x_u8, idx=idx_identity, y=y_u8,
+                         prep_backward=True, loss=self.loss, **kw)
+        if self.world_size == 1:
+            ops.step_backward(self.params, self.ws, b, images=x_u8, idx=idx_identity, lr=self.lr)
+        else:
+            import torch.distributed as dist
+            ops.step_backward(self.params, self.ws, b, images=x_u8, idx=idx_identity, grads=self.grads,
+                              grad_scale=1.0 / self.world_size)
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
+            ops.sgd_step(self.params, self.grads, self.lr)
+
+    def eval_step(self, resident, idx: torch.Tensor) -> None:
+        """Validation forward (mp:472-481): eval mode, loss only, accumulates loss[1]."""
+        ops.step_forward(self.params, self.ws, idx.numel(), images=resident.images, labels=resident.labels,
+                         idx=idx, loss=self.loss)
+
+    def zero_epoch_loss(self) -> None:
+        self.loss.zero_()
+
+    def epoch_loss(self) -> float:
+        """Host read (one sync): sum over batches of mean_loss_b / B_b (mp:465, 481)."""
+        return float(self.loss[1].item())
+
+    def last_batch_loss(self) -> float:
+        return float(self.loss[0].item())
+
+    # ------------------------------------------------------------------ CUDA graph of K steps
+    def capture_steps(self, resident, idx_batches: Sequence[torch.Tensor],
+                      masks: Optional[Sequence[torch.Tensor]] = None, philox_step0: int = 0
+                      ) -> torch.cuda.CUDAGraph:
+        """Capture the given steps, unrolled, into one CUDA graph (the batch-64 regime is
+        launch-bound: 3 kernels of a few microseconds per step).  The graph reads `idx_batches`'
+        storage at replay time, so refilling that storage replays the same steps on new indices."""
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.grads, group=self.group)          # warm NCCL outside the capture
+            self.grads.zero_()
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        saved = self.step_count
+        with torch.cuda.graph(g):
+            for t, idx in enumerate(idx_batches):
+                self.train_step(resident, idx, mask=None if masks is None else masks[t],
+                                philox_step=philox_step0 + t)
+        self.step_count = saved + len(idx_batches)
+        return g
