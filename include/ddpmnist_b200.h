@@ -116,6 +116,37 @@ int ddpm_step_backward(float* d_params,
                        const float* d_dlogits, int batch, float grad_scale, float lr,
                        float* d_grads, void* d_workspace, void* stream);
 
+/* Forward/eval step for callers that cannot allocate.  No counterpart in the reference (added for
+ * embedding; the reference is a script that allocates freely through torch).
+ *
+ * Who needs it: a host that hands a plug-in its input and output buffers and nothing else — a
+ * validation hook inside another framework's pipeline whose memory pool is closed to plug-ins, a C
+ * harness that must not call cudaMalloc once running because cudaMalloc synchronises the device,
+ * a process held to a fixed device-memory budget.  Such a caller has no workspace to give
+ * ddpm_step_forward, so this variant keeps the scratch inside the library: a fixed
+ * 3,490,816-byte device array (sized for DDPM_STATIC_SCRATCH_MAX_BATCH rows) that every GPU which
+ * loads the library holds until the process exits.  The call path performs no cudaMalloc/cudaFree
+ * and uses no allocating library routine; inputs and outputs are still the caller's.
+ *
+ * Same arguments and results as ddpm_step_forward, minus d_workspace, with these limits:
+ *   - batch > DDPM_STATIC_SCRATCH_MAX_BATCH is rejected (non-zero return, message says so);
+ *   - forward/eval only: DDPM_FWD_PREP_BACKWARD is rejected, because ddpm_step_backward reads a
+ *     caller-owned workspace;
+ *   - the first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current); make that first call before starting any
+ *     stream capture;
+ *   - all calls on a device share the one array, which still holds the previous call's contents;
+ *     the entry point re-zeroes the control words it depends on at every call, but two calls
+ *     that overlap on the GPU (different streams, or different host threads) race on it —
+ *     serialise them. */
+#define DDPM_STATIC_SCRATCH_MAX_BATCH 128
+int ddpm_step_forward_static_scratch(const float* d_params,
+                      const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                      const int64_t* d_idx, const float* d_x, const uint8_t* d_y,
+                      const uint8_t* d_mask, uint64_t philox_seed, uint64_t philox_step,
+                      int batch, unsigned flags,
+                      float* d_logits, float* d_loss, void* stream);
+
 /* K4 alone. nn.CrossEntropyLoss()(logits, y) forward + gradient (mp:444, 461): d_loss[0] = mean
  * NLL of log_softmax; d_dlogits = (softmax - onehot)/batch (may be NULL).  y is uint8. */
 int ddpm_cross_entropy(const float* d_logits, const uint8_t* d_y, int batch,

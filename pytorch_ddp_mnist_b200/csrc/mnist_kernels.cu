@@ -904,3 +904,64 @@ int ddpm_sgd_step(float* d_params, const float* d_grads, int64_t n, float lr, fl
 }
 
 }  // extern "C"
+
+// ==========================================================================================
+// Forward/eval entry point that owns its scratch (no allocation anywhere on the call path)
+// ==========================================================================================
+// Some hosts hand a plug-in its input and output buffers and nothing else: a validation hook
+// inside another framework's data pipeline whose memory pool is closed to plug-ins, a C harness
+// that may not call cudaMalloc after start-up because cudaMalloc synchronises the whole device,
+// a process running under a fixed device-memory budget.  Such a caller cannot provide the
+// workspace ddpm_step_forward needs.  For them the scratch lives here, in a fixed-size device
+// array that every GPU loading this library carries until the process exits.
+//
+// g_static_scratch is a HOST-side handle in host code, not a device address.  The address is
+// looked up once per device with cudaGetSymbolAddress while that device is current, and that
+// pointer is what the kernels receive.
+namespace ddpm {
+
+constexpr size_t STATIC_SCRATCH_BYTES = 3490816;   // == ddpm_workspace_bytes(DDPM_STATIC_SCRATCH_MAX_BATCH)
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+static void* g_static_scratch_ptr[64] = {};        // per device, filled on first use
+
+static int static_scratch_for_current_device(void** out) {
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    DDPM_CHECK_ARG(dev >= 0 && dev < 64, "static scratch: device ordinal %d not supported", dev);
+    void* p = __atomic_load_n(&g_static_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        DDPM_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        DDPM_CHECK_ARG(p != nullptr && ((uintptr_t)p & 255) == 0, "static scratch: bad symbol address");
+        __atomic_store_n(&g_static_scratch_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+
+}  // namespace ddpm
+
+extern "C" int ddpm_step_forward_static_scratch(
+        const float* d_params,
+        const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+        const int64_t* d_idx, const float* d_x, const uint8_t* d_y,
+        const uint8_t* d_mask, uint64_t philox_seed, uint64_t philox_step,
+        int batch, unsigned flags, float* d_logits, float* d_loss, void* stream) {
+    DDPM_CHECK_ARG(batch > 0, "ddpm_step_forward_static_scratch: batch must be positive (got %d)", batch);
+    DDPM_CHECK_ARG(batch <= DDPM_STATIC_SCRATCH_MAX_BATCH,
+                   "ddpm_step_forward_static_scratch: batch %d exceeds the built-in scratch limit of %d rows; "
+                   "use ddpm_step_forward with a caller-provided workspace", batch, DDPM_STATIC_SCRATCH_MAX_BATCH);
+    DDPM_CHECK_ARG((flags & DDPM_FWD_PREP_BACKWARD) == 0,
+                   "ddpm_step_forward_static_scratch: forward/eval only (DDPM_FWD_PREP_BACKWARD needs a "
+                   "caller-owned workspace that ddpm_step_backward can read)");
+    DDPM_CHECK_ARG(ws_layout(batch).total <= STATIC_SCRATCH_BYTES,
+                   "ddpm_step_forward_static_scratch: internal scratch too small for batch %d", batch);
+    void* scratch = nullptr;
+    if (static_scratch_for_current_device(&scratch)) return 1;
+    // The array keeps whatever the previous call left.  Only the control words must start at
+    // zero (the ticket counter that elects the block summing the per-row losses); everything
+    // else is written before it is read.
+    DDPM_CUDA(cudaMemsetAsync(scratch, 0, 64 * sizeof(uint32_t), (cudaStream_t)stream));
+    return ddpm_step_forward(d_params, d_images, d_labels, n_samples, d_idx, d_x, d_y, d_mask,
+                             philox_seed, philox_step, batch, flags, d_logits, d_loss, scratch, stream);
+}
