@@ -1,0 +1,64 @@
+"""Run under torchrun with 2 ranks (tests/test_gpu_train.py::test_multi_gpu_ddp_matches_reference_ws2):
+the engine's DDP path (pre-divided flat bucket + NCCL allreduce SUM + flat SGD) against the
+reference's own 2-rank gloo run recorded in tests/golden/traj_ws2.npz."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+
+from oracle import mnist_oracle as O                      # noqa: E402
+from pytorch_ddp_mnist_b200 import engine as E, synth     # noqa: E402
+from pytorch_ddp_mnist_b200.dataset import ResidentDataset  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", init_method="env://", device_id=dev)
+    g = np.load(os.path.join(REPO, "tests", "golden", "traj_ws2.npz"))
+    im, lb = synth.synth(synth.TRAIN_N, synth.TRAIN_SEED)
+    res = ResidentDataset.from_arrays(im, lb, dev)
+    eng = E.TrainEngine(dev, 64, world_size=world, rank=rank)
+    torch.manual_seed(100 + rank)                          # ranks start different, like the reference
+    eng.load_state_dict(E.init_params_like_reference())
+    if rank == 0:
+        eng.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
+    eng.broadcast_params(0)                                # DDP wrap: everyone adopts rank 0's
+    masks = torch.from_numpy(O.unpack_masks(g[f"rank{rank}.masks"])).to(dev)
+    idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
+    assert np.array_equal(g[f"rank{rank}.idx"][0], O.shard_indices(60000, world, rank)[:64])
+    losses = []
+    for t in range(idx.shape[0]):
+        eng.train_step(res, idx[t], mask=masks[t])
+        losses.append(eng.last_batch_loss())
+        if t == 0:
+            pass
+    ref = g[f"rank{rank}.losses"]
+    err = np.abs(np.array(losses) - ref).max()
+    assert err < 5e-3 * np.abs(ref).max(), (rank, err)
+    assert np.abs(np.array(losses[:3]) - ref[:3]).max() < 1e-5
+    pu = O.unflatten_params(eng.params.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        r = g[f"paramsN.{k}"].astype(np.float64)
+        fro = np.linalg.norm(pu[k] - r) / np.linalg.norm(r)
+        assert fro < 5e-3, (k, fro)
+    # replicas stay bit-identical
+    mine = eng.params.clone()
+    other = mine.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(mine, other), "replicas diverged"
+    dist.barrier()
+    if rank == 0:
+        print("MULTIGPU_OK max loss err %.2e" % err)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,202 @@
+"""Drop-in surface on the GPU: loaders, create_model/loss/optimizer with the reference's loop body,
+and `main()` end to end against what the UNMODIFIED reference `main()` produced (tests/golden/main_e2e.npz)."""
+import io
+import contextlib
+import os
+import re
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from oracle import mnist_oracle as O           # noqa: E402  (checker only)
+from oracle.determinism import mask_for_step   # noqa: E402
+
+TOL_TRAJ = 5e-3
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+def _fro(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+@pytest.fixture(scope="module")
+def nc_dir(tmp_path_factory):
+    from pytorch_ddp_mnist_b200 import synth
+    d = tmp_path_factory.mktemp("nc_e2e")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "main_e2e.npz"))
+    synth.write_default_files(str(d), int(g["train_n"]), int(g["test_n"]))
+    return str(d)
+
+
+def test_resident_dataset_from_file_and_loader(dev, nc_dir):
+    from pytorch_ddp_mnist_b200 import synth
+    from pytorch_ddp_mnist_b200.dataset import DeviceBatchLoader, MNISTNetCDF, ResidentDataset
+    im, lb = synth.synth(4000, synth.TRAIN_SEED)
+    r = ResidentDataset.from_file(os.path.join(nc_dir, "mnist_train_images.nc"), dev, chunk_rows=1024)
+    assert np.array_equal(r.images.cpu().numpy().reshape(-1, 28, 28), im)
+    assert np.array_equal(r.labels.cpu().numpy(), lb)
+    with contextlib.redirect_stdout(io.StringIO()):
+        ds = MNISTNetCDF(nc_dir, is_train=True, transforms=True, device=dev)
+    assert len(ds) == 4000
+    x, y = ds[17]                                         # mp:39-49 contract
+    assert x.shape == (1, 28, 28) and x.dtype == torch.float32 and y.dtype == np.uint8 and y.shape == ()
+    assert np.array_equal(x.cpu().numpy().reshape(-1).view(np.uint32), O.decode_lut()[im[17].reshape(-1)].view(np.uint32))
+    assert y == lb[17]
+    from torch.utils.data import DistributedSampler
+    from pytorch_ddp_mnist_b200.dataset import _IndexOnly
+    s = DistributedSampler(_IndexOnly(4000), num_replicas=2, rank=1, shuffle=True, seed=42)
+    loader = DeviceBatchLoader(ds, batch_size=64, sampler=s)
+    s.set_epoch(0)
+    shard = O.shard_indices(4000, 2, 1, 0)
+    batches = list(loader)
+    assert len(batches) == len(loader) == 32 and batches[-1][0].shape[0] == 2000 - 31 * 64
+    xb, yb = batches[3]
+    xr, yr = O.gather_decode(im, lb, shard[3 * 64:4 * 64])
+    assert xb.shape == (64, 1, 28, 28) and yb.dtype == torch.uint8
+    assert np.array_equal(xb.cpu().numpy().reshape(64, 784).view(np.uint32), xr.view(np.uint32))
+    assert np.array_equal(yb.cpu().numpy(), yr)
+
+
+def test_reference_loop_body_with_dropin_objects(dev, golden, synth_train):
+    """mp:453-466 written out with this package's create_model / CrossEntropyLoss / SGD."""
+    from pytorch_ddp_mnist_b200.dataset import DeviceBatchLoader, ResidentDataset
+    from pytorch_ddp_mnist_b200.model import SGD, CrossEntropyLoss, create_model
+    g = golden["traj_ws1"]
+    im, lb = synth_train
+    res = ResidentDataset.from_arrays(im, lb, dev)
+    torch.manual_seed(0)
+    model = create_model()
+    assert list(model.state_dict().keys()) == list(O.PARAM_KEYS)
+    for k in O.PARAM_KEYS:                                   # same init as the reference under the same seed
+        assert np.array_equal(model.state_dict()[k].numpy(), g[f"params0.{k}"]), k
+    device = dev
+    model = model.to(device)
+    model.set_mask_provider(lambda t, b: mask_for_step(t, b))
+    optimizer = SGD(model.parameters(), lr=0.01)
+    loss = CrossEntropyLoss()
+    from torch.utils.data import DistributedSampler
+    from pytorch_ddp_mnist_b200.dataset import _IndexOnly
+    sampler = DistributedSampler(_IndexOnly(60000), num_replicas=1, rank=0, shuffle=True, seed=42)
+    train_loader = DeviceBatchLoader(res, batch_size=64, sampler=sampler)
+    model.train()
+    train_loader.sampler.set_epoch(0)
+    epoch_loss = 0
+    losses = []
+    for n, (x, y) in enumerate(train_loader):
+        if n == 30:
+            break
+        x = x.to(device, non_blocking=True)
+        y = y.to(device, non_blocking=True)
+        x = x.view(x.shape[0], -1)
+        optimizer.zero_grad()
+        y_hat = model(x)
+        batch_loss = loss(y_hat, y)
+        batch_loss.backward()
+        optimizer.step()
+        batch_loss_scalar = batch_loss.item()
+        epoch_loss += batch_loss_scalar / x.shape[0]
+        losses.append(batch_loss_scalar)
+    assert np.abs(np.array(losses[:5]) - g["losses"][:5]).max() < 1e-5
+    assert np.abs(np.array(losses) - g["losses"][:30]).max() < TOL_TRAJ * 2.4
+    # eval mode + no_grad (mp:469-477)
+    with torch.no_grad():
+        model.eval()
+        x, y = next(iter(train_loader))
+        v = loss(model(x.view(x.shape[0], -1)), y).item()
+    sd = {k: t.detach().cpu().numpy() for k, t in model.state_dict().items()}
+    xr, yr = O.gather_decode(im, lb, O.shard_indices(60000, 1, 0)[:64])
+    assert abs(v - float(O.eval_loss(sd, xr, yr))) < 2e-5
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        model(torch.zeros(2, 784))
+
+
+def test_main_end_to_end_matches_unmodified_reference(dev, golden, nc_dir):
+    """`main()` on the engine vs the reference's own `main()` (2 epochs, 4000/1000 samples,
+    batch 64, short last batches, shuffled validation loader): same printed lines to 4 decimals
+    within tolerance, same final state_dict."""
+    from pytorch_ddp_mnist_b200 import train
+    g = golden["main_e2e"]
+    config = train.configure(["--batch_size", str(int(g["batch"])), "--n_epochs", str(int(g["epochs"]))])
+    config["trainer"].update(rank=0, world_size=1, device=dev)
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        train_loader, test_loader = train.create_data_loaders(config, None, dataset_loc=nc_dir, device=dev)
+        torch.manual_seed(0)
+        model = train.main(train.create_model(), train_loader, test_loader, config,
+                           mask_fn=lambda t, b: mask_for_step(t, b))
+    lines = re.findall(r"Epoch=(\d+), train_loss=([0-9.]+), val_loss=([0-9.]+)", buf.getvalue())
+    got = np.array([[float(a), float(b), float(c)] for a, b, c in lines])
+    want = g["epoch_lines"]
+    assert got.shape == want.shape == (2, 3)
+    assert np.abs(got[:, 1:] - want[:, 1:]).max() <= TOL_TRAJ * np.abs(want[:, 1:]).max() + 1e-4, (got, want)
+    sd = model.state_dict()
+    assert list(sd.keys()) == list(O.PARAM_KEYS)
+    for k in O.PARAM_KEYS:
+        assert _fro(sd[k].cpu().numpy(), g[f"state.{k}"]) < TOL_TRAJ, k
+
+
+def test_engine_graph_replay_equals_eager(dev, golden, synth_train):
+    from pytorch_ddp_mnist_b200 import engine as E
+    from pytorch_ddp_mnist_b200.dataset import ResidentDataset
+    g = golden["traj_ws1"]
+    im, lb = synth_train
+    res = ResidentDataset.from_arrays(im, lb, dev)
+    sd = {k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS}
+    idx = torch.from_numpy(g["idx"][:20].reshape(-1)).to(dev)
+    outs = []
+    for graphed in (False, True):
+        eng = E.TrainEngine(dev, 64)
+        eng.load_state_dict(sd)
+        batches = list(torch.split(idx.clone(), 64))
+        if graphed:
+            gr = eng.capture_steps(res, batches)
+            eng.load_state_dict(sd)                 # capture ran nothing; make sure
+            eng.zero_epoch_loss()
+            gr.replay()
+        else:
+            for t, b in enumerate(batches):
+                eng.train_step(res, b, philox_step=t)
+        torch.cuda.synchronize()
+        outs.append((eng.params.clone(), float(eng.loss[1])))
+    assert torch.equal(outs[0][0], outs[1][0]) and abs(outs[0][1] - outs[1][1]) < 1e-6
+
+
+def test_checkpoint_roundtrip(dev, tmp_path, golden):
+    from pytorch_ddp_mnist_b200 import engine as E
+    g = golden["traj_ws1"]
+    eng = E.TrainEngine(dev, 8)
+    eng.load_state_dict({k: torch.from_numpy(g[f"paramsN.{k}"]) for k in O.PARAM_KEYS})
+    p = str(tmp_path / "model.pt")
+    torch.save(eng.state_dict(), p)                          # mp:510-511
+    sd = torch.load(p)
+    assert list(sd.keys()) == list(O.PARAM_KEYS)
+    ref = torch.nn.Sequential(torch.nn.Linear(784, 128), torch.nn.ReLU(), torch.nn.Dropout(0.2),
+                              torch.nn.Linear(128, 128), torch.nn.ReLU(), torch.nn.Linear(128, 10, bias=False))
+    ref.load_state_dict(sd)                                   # loads into the reference's architecture
+    eng2 = E.TrainEngine(dev, 8)
+    eng2.load_state_dict(sd)
+    assert torch.equal(eng.params, eng2.params)
+
+
+def test_multi_gpu_ddp_matches_reference_ws2(dev):
+    """2 ranks over NCCL vs the reference's 2-rank gloo run (tests/golden/traj_ws2.npz)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29733",
+                          os.path.join(here, "multigpu_check.py")], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "MULTIGPU_OK" in out.stdout
