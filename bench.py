@@ -244,8 +244,15 @@ def main() -> None:
             line["cpu_baseline"] = _cpu_baseline(args)
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Tear-down must never hang the run: NCCL communicators captured in live CUDA graphs have
+        # been seen to block in destroy_process_group().  The JSON line is already flushed, so give
+        # the orderly path a few seconds and then leave.
+        sys.stdout.flush()
+        threading.Timer(20.0, lambda: os._exit(0)).start()
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        del graph
+        os._exit(0)
 
 
 def _time_kernels(torch, ops, eng, resident, shard_dev, B, world):
@@ -313,7 +320,7 @@ def _time_e2e(torch, eng, im, lb, shard, B, steps, world, dev, dist):
     pixels + labels from pinned memory, the fused step, and a D2H read of the loss."""
     import numpy as np
     steps = max(steps, 10)
-    rows = shard[: (steps + 10) * B].numpy() % im.shape[0]
+    rows = np.resize(shard.numpy(), (steps + 10) * B) % im.shape[0]      # wraps if the shard is shorter
     host_x = torch.from_numpy(im.reshape(-1, 784)[rows]).pin_memory()
     host_y = torch.from_numpy(lb[rows]).pin_memory()
     x_dev = [torch.empty(B, 784, dtype=torch.uint8, device=dev) for _ in range(2)]
