@@ -119,7 +119,8 @@ def _config(args, extra=None):
          "batch_per_rank": args.batch, "dataset_samples": BENCH_N,
          "l2": "resident u8 dataset is 188 MB (> 126 MB L2) and every step gathers rows not touched before; "
                "weights stay L2-resident as in any training loop",
-         "graph_chunk_steps": CHUNK}
+         "steps_per_launch_or_graph": CHUNK,
+         "step_kernel": "three-kernel (v1)" if args.three_kernel or args.batch > 512 else "persistent (v2)"}
     if extra:
         c.update(extra)
     return c
@@ -134,6 +135,7 @@ def main() -> None:
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--three-kernel", action="store_true", help="use the v1 three-kernel step instead of the persistent kernel")
     ap.add_argument("--cpu-baseline-steps", type=int, default=150)
     args = ap.parse_args()
     if args.warmup < 3:
@@ -176,30 +178,46 @@ def main() -> None:
     eng.load_state_dict(E.init_params_like_reference())
     eng.broadcast_params()
 
-    # ---- graph of CHUNK unrolled steps reading a fixed index buffer that is refilled per replay
+    # ---- ws == 1: the persistent kernel runs CHUNK whole steps per launch straight off the shard.
+    # ---- ws  > 1: CUDA graph of CHUNK unrolled steps (persistent 1-step kernel -> NCCL allreduce ->
+    #      flat SGD) reading a fixed index buffer that is refilled per replay.
     chunk = min(CHUNK, K)
+    persistent = (B <= 512) and not args.three_kernel
     idx_buf = torch.empty(chunk * B, dtype=torch.int64, device=dev)
     idx_buf.copy_(shard_dev[:chunk * B])
     batches = list(torch.split(idx_buf, B))
-    for t in range(3):                                      # eager warm-up (also warms NCCL)
-        eng.train_step(resident, batches[t % chunk])
-    graph = eng.capture_steps(resident, batches)
-    kernels_per_step = 3 if world == 1 else 4               # fc1_fwd, rows, grads (+ sgd); NCCL's kernel not counted
+    for t in range(3):                                      # eager warm-up (also warms NCCL, sets func attributes)
+        if persistent:
+            eng.train_steps(resident, batches[t % chunk], B, 1)
+        else:
+            eng.train_step(resident, batches[t % chunk])
+    use_graph = (world > 1) or not persistent
+    graph = eng.capture_steps(resident, batches, persistent=persistent) if use_graph else None
+    if persistent:
+        kernels_per_chunk = 1 if world == 1 else 2 * chunk   # persistent (+ sgd per step); NCCL's kernel not counted
+    else:
+        kernels_per_chunk = (3 if world == 1 else 4) * chunk
 
     def run(n_steps: int, start_step: int) -> int:
         """n_steps optimisation steps starting at global step `start_step`; returns launches."""
         done, launches = 0, 0
         while done + chunk <= n_steps:
             s = (start_step + done) * B
-            idx_buf.copy_(shard_dev[s:s + chunk * B])
-            graph.replay()
+            if use_graph:
+                idx_buf.copy_(shard_dev[s:s + chunk * B])
+                graph.replay()
+            else:
+                eng.train_steps(resident, shard_dev[s:s + chunk * B], B, chunk)
             done += chunk
-            launches += chunk * kernels_per_step
+            launches += kernels_per_chunk
         while done < n_steps:                               # remainder, eager
             s = (start_step + done) * B
-            eng.train_step(resident, shard_dev[s:s + B])
+            if persistent:
+                eng.train_steps(resident, shard_dev[s:s + B], B, 1)
+            else:
+                eng.train_step(resident, shard_dev[s:s + B])
             done += 1
-            launches += kernels_per_step
+            launches += kernels_per_chunk // chunk if (world > 1 or not persistent) else 1
         return launches
 
     run(W, 0)
@@ -227,7 +245,7 @@ def main() -> None:
     final_loss = eng.last_batch_loss()
 
     # ---- per-kernel durations, live, with CUDA events on the launching stream
-    kern = _time_kernels(torch, ops, eng, resident, shard_dev, B, world)
+    kern = _time_kernels(torch, ops, eng, resident, shard_dev, B, world, three_kernel=not persistent)
 
     # ---- e2e: host buffers in, loss out, every step
     e2e = _time_e2e(torch, eng, im, lb, shard, B, min(K, 2000), world, dev, dist if world > 1 else None)
@@ -251,11 +269,11 @@ def main() -> None:
         threading.Timer(20.0, lambda: os._exit(0)).start()
         torch.cuda.synchronize()
         dist.barrier()
-        del graph
+        graph = None
         os._exit(0)
 
 
-def _time_kernels(torch, ops, eng, resident, shard_dev, B, world):
+def _time_kernels(torch, ops, eng, resident, shard_dev, B, world, three_kernel=False):
     """Average duration of each of the step's kernels, measured with CUDA events around runs of
     that kernel alone on fresh (cold) rows, and the HBM roofline of the dominant one.
     Algorithmic bytes per launch: pixels 784 B + index 8 B (+ label 1 B) per image,
@@ -299,7 +317,28 @@ def _time_kernels(torch, ops, eng, resident, shard_dev, B, world):
     bytes_fwd = B * (784 + 8 + 1) + (100_352 + 128) * 4 + 71_680 + 4 * B * 512 + B * 64   # px,idx,label + W1,b1 + W2,b2,W3 + h1d,h2,dz2,dz1 + dz3
     bytes_bwd = B * (784 + 8) + 4 * B * 512 + B * 64 + 2 * P + (P if world > 1 else 0)    # px again + activations + params r/w (+ bucket)
     bytes_gather = B * (784 + 8 + 1) + B * (3136 + 1)
+    # persistent kernel: 50 steps per launch, average per step
+    t_persist = None
+    if B <= 512:
+        nst = 50
+        flat = shard_dev[:nst * B * 4]
+
+        def persist(i):
+            ops.train_steps_persistent(params, eng.ws, B, nst, images=resident.images, labels=resident.labels,
+                                       idx=flat[(i % 4) * nst * B:((i % 4) + 1) * nst * B], philox=(1, 0), lr=eng.lr)
+        for i in range(3):
+            persist(i)
+        torch.cuda.synchronize()
+        ev[2].record()
+        for i in range(8):
+            persist(i)
+        ev[3].record()
+        torch.cuda.synchronize()
+        t_persist = ev[2].elapsed_time(ev[3]) / (8 * nst)
+    bytes_step = B * (784 + 8 + 1) + 2 * P          # pixels + index + label, parameters read once and written once
     kernels = [
+        {"name": "train_persist_kernel (whole step: fwd + loss + bwd + SGD; per step of a 50-step launch)",
+         "ms": t_persist, "alg_bytes": bytes_step, "gbs": (bytes_step / t_persist / 1e6) if t_persist else None},
         {"name": "step_forward (fc1_fwd_kernel + rows_kernel)", "ms": t_fwd, "alg_bytes": bytes_fwd,
          "gbs": bytes_fwd / t_fwd / 1e6},
         {"name": "step_backward (grads_kernel, SGD fused)" if world == 1 else "step_backward (grads_kernel -> bucket)",
@@ -307,11 +346,11 @@ def _time_kernels(torch, ops, eng, resident, shard_dev, B, world):
         {"name": "gather_decode_kernel (standalone loader kernel, not in the fused step)", "ms": t_gather,
          "alg_bytes": bytes_gather, "gbs": bytes_gather / t_gather / 1e6},
     ]
-    dom = max(kernels[:2], key=lambda k: k["ms"])
+    dom = kernels[0] if (t_persist and not three_kernel) else max(kernels[1:3], key=lambda k: k["ms"])
     roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": hbm, "unit": "GB/s", "frac": dom["gbs"] / hbm,
             "traffic": None, "kernel": dom["name"], "peak_source": which,
-            "note": "host-launched back to back (includes launch gaps); batch-64 steps are launch/latency-bound, "
-                    "see DESIGN.md §4"}
+            "note": "algorithmic bytes = what one step must move (DESIGN.md §4); batch-64 steps are latency-bound "
+                    "(2 grid barriers + dependent round trips per step), not bandwidth-bound"}
     return {"kernels": kernels, "roofline": roof}
 
 

@@ -116,6 +116,26 @@ int ddpm_step_backward(float* d_params,
                        const float* d_dlogits, int batch, float grad_scale, float lr,
                        float* d_grads, void* d_workspace, void* stream);
 
+/* Persistent step kernel (small-batch fast path): ONE cooperative launch runs `nsteps` complete
+ * optimisation steps — the loop body mp:455-463 repeated — with the fc1 weights held in shared
+ * memory across steps (see csrc/persist_kernel.cu).  Same arithmetic contract as
+ * ddpm_step_forward(PREP_BACKWARD) + ddpm_step_backward, other summation order.
+ *   d_idx        i64[nsteps*batch]   consecutive batches of the shard (the DataLoader's chunks, mp:396-401)
+ *   d_masks      u8[nsteps][batch][128] injected dropout masks, or NULL with DDPM_FWD_PHILOX_MASK
+ *                (step s uses Philox counter philox_step0 + s), or NULL without the flag = no dropout
+ *   d_grads      f32[118272] or NULL: gradient bucket scaled by grad_scale (DDP: 1/world_size)
+ *   lr           != 0: SGD fused, d_params updated after every step; == 0: gradients only
+ *   d_loss       f32[2] as in ddpm_step_forward (may be NULL); d_loss_steps f32[nsteps] per-step
+ *                mean loss (may be NULL)
+ * batch must be <= 512 (larger batches are compute-bound: use the step_forward/backward pair).
+ * The device must be able to co-schedule the kernel's 123 blocks (any B200 does). */
+int ddpm_train_steps_persistent(float* d_params, float* d_grads,
+                                const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                                const int64_t* d_idx, const uint8_t* d_masks,
+                                uint64_t philox_seed, uint64_t philox_step0,
+                                int batch, int nsteps, unsigned flags, float grad_scale, float lr,
+                                float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);
+
 /* Forward/eval step for callers that cannot allocate.  No counterpart in the reference (added for
  * embedding; the reference is a script that allocates freely through torch).
  *

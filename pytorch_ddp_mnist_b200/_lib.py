@@ -17,6 +17,7 @@ IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
 FWD_PREP_BACKWARD, FWD_PHILOX_MASK = 1, 2
 STATIC_SCRATCH_MAX_BATCH = 128
+PERSIST_MAX_BATCH = 512
 ABI_VERSION = 1
 
 
@@ -49,6 +50,8 @@ SIGNATURES = {
                                  _vp, _vp, _vp, _vp]),
     "ddpm_step_forward_static_scratch": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _u64, _u64, _i32,
                                                 _u32, _vp, _vp, _vp]),
+    "ddpm_train_steps_persistent": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32,
+                                           _f32, _f32, _vp, _vp, _vp, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),

@@ -72,7 +72,9 @@ static WsLayout ws_layout_compute(int max_batch) {
     size_t off = 0;
     const size_t B = (size_t)max_batch;
     L.ctrl = off;    off = al256(off + 64 * sizeof(uint32_t));
-    L.part1 = off;   off = al256(off + part1_rows_capacity(max_batch) * HID * sizeof(float));
+    size_t part_rows = part1_rows_capacity(max_batch);
+    if (part_rows < (size_t)14 * B) part_rows = (size_t)14 * B;      // persistent kernel: 14 pixel-tile partials
+    L.part1 = off;   off = al256(off + part_rows * HID * sizeof(float));
     L.h1d = off;     off = al256(off + B * HID * sizeof(float));
     L.h2 = off;      off = al256(off + B * HID * sizeof(float));
     L.dz2 = off;     off = al256(off + B * HID * sizeof(float));

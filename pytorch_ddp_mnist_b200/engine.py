@@ -105,22 +105,49 @@ class TrainEngine:
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
             ops.sgd_step(self.params, self.grads, self.lr)
 
-    def train_step_host_batch(self, x_u8: torch.Tensor, y_u8: torch.Tensor, idx_identity: torch.Tensor,
-                              mask: Optional[torch.Tensor] = None) -> None:
-        """Same step for a batch that was just copied from host memory (u8 [B,784] + u8 [B])."""
-        b = x_u8.shape[0]
-        kw = dict(mask=mask) if mask is not None else dict(philox=(self.seed, self.step_count))
-        self.step_count += 1
-        ops.step_forward(self.params, self.ws, b, images=x_u8, idx=idx_identity, y=y_u8,
-                         prep_backward=True, loss=self.loss, **kw)
+    def train_steps(self, resident, idx_flat: torch.Tensor, batch: int, nsteps: int,
+                    masks: Optional[torch.Tensor] = None, philox_step0: Optional[int] = None,
+                    loss_steps: Optional[torch.Tensor] = None) -> None:
+        """`nsteps` consecutive optimisation steps over `idx_flat` (i64[nsteps*batch], device).
+        batch <= 512: the persistent kernel — ONE launch for all steps at ws == 1; at ws > 1 one
+        launch per step writes the pre-divided bucket, then allreduce + flat SGD.  Larger batches
+        fall back to the three-kernel step."""
+        from ._lib import PERSIST_MAX_BATCH
+        st0 = self.step_count if philox_step0 is None else philox_step0
+        self.step_count += nsteps
+        if batch > PERSIST_MAX_BATCH:
+            for t in range(nsteps):
+                self.step_count -= 1
+                self.train_step(resident, idx_flat[t * batch:(t + 1) * batch],
+                                mask=None if masks is None else masks[t], philox_step=st0 + t)
+            return
+        kw = dict(images=resident.images, labels=resident.labels)
         if self.world_size == 1:
-            ops.step_backward(self.params, self.ws, b, images=x_u8, idx=idx_identity, lr=self.lr)
-        else:
-            import torch.distributed as dist
-            ops.step_backward(self.params, self.ws, b, images=x_u8, idx=idx_identity, grads=self.grads,
-                              grad_scale=1.0 / self.world_size)
+            mk = dict(masks=masks) if masks is not None else dict(philox=(self.seed, st0))
+            ops.train_steps_persistent(self.params, self.ws, batch, nsteps, idx=idx_flat, lr=self.lr,
+                                       loss=self.loss, loss_steps=loss_steps, **mk, **kw)
+            return
+        import torch.distributed as dist
+        for t in range(nsteps):
+            mk = dict(masks=masks[t:t + 1]) if masks is not None else dict(philox=(self.seed, st0 + t))
+            ops.train_steps_persistent(self.params, self.ws, batch, 1, idx=idx_flat[t * batch:(t + 1) * batch],
+                                       grads=self.grads, grad_scale=1.0 / self.world_size, lr=0.0, loss=self.loss,
+                                       loss_steps=None if loss_steps is None else loss_steps[t:t + 1], **mk, **kw)
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
             ops.sgd_step(self.params, self.grads, self.lr)
+
+    def train_step_host_batch(self, x_u8: torch.Tensor, y_u8: torch.Tensor, idx_identity: torch.Tensor,
+                              mask: Optional[torch.Tensor] = None) -> None:
+        """Same step for a batch that was just copied from host memory (u8 [B,784] + u8 [B]):
+        the staged batch is used as a B-sample dataset indexed by `idx_identity` = arange(B)."""
+        class _Staged:
+            images, labels = x_u8, y_u8
+        b = x_u8.shape[0]
+        from ._lib import PERSIST_MAX_BATCH
+        if b <= PERSIST_MAX_BATCH:
+            self.train_steps(_Staged, idx_identity, b, 1, masks=None if mask is None else mask[None])
+        else:
+            self.train_step(_Staged, idx_identity, mask=mask)
 
     def eval_step(self, resident, idx: torch.Tensor) -> None:
         """Validation forward (mp:472-481): eval mode, loss only, accumulates loss[1]."""
@@ -139,8 +166,8 @@ class TrainEngine:
 
     # ------------------------------------------------------------------ CUDA graph of K steps
     def capture_steps(self, resident, idx_batches: Sequence[torch.Tensor],
-                      masks: Optional[Sequence[torch.Tensor]] = None, philox_step0: int = 0
-                      ) -> torch.cuda.CUDAGraph:
+                      masks: Optional[Sequence[torch.Tensor]] = None, philox_step0: int = 0,
+                      persistent: bool = False) -> torch.cuda.CUDAGraph:
         """Capture the given steps, unrolled, into one CUDA graph (the batch-64 regime is
         launch-bound: 3 kernels of a few microseconds per step).  The graph reads `idx_batches`'
         storage at replay time, so refilling that storage replays the same steps on new indices."""
@@ -153,7 +180,11 @@ class TrainEngine:
         saved = self.step_count
         with torch.cuda.graph(g):
             for t, idx in enumerate(idx_batches):
-                self.train_step(resident, idx, mask=None if masks is None else masks[t],
-                                philox_step=philox_step0 + t)
+                if persistent:
+                    self.train_steps(resident, idx, idx.numel(), 1,
+                                     masks=None if masks is None else masks[t][None], philox_step0=philox_step0 + t)
+                else:
+                    self.train_step(resident, idx, mask=None if masks is None else masks[t],
+                                    philox_step=philox_step0 + t)
         self.step_count = saved + len(idx_batches)
         return g

@@ -12,7 +12,7 @@ from . import _lib
 from ._lib import CLASSES, HID, IN, N_PARAMS, check, cur_stream, lib, ptr
 
 __all__ = ["decode_lut", "gather_decode", "dropout_mask_philox", "Workspace", "step_forward",
-           "step_backward", "cross_entropy", "sgd_step"]
+           "step_backward", "train_steps_persistent", "cross_entropy", "sgd_step"]
 
 
 def _need(t: Optional[torch.Tensor], name: str, dtype, shape=None, optional=False):
@@ -134,6 +134,35 @@ def step_backward(params: torch.Tensor, ws: Workspace, batch: int, *,
         n = images.shape[0]
     check(lib.ddpm_step_backward(ptr(params), ptr(images), n, ptr(idx), ptr(x), ptr(dlogits), batch,
                                  grad_scale, lr, ptr(grads), ptr(ws.buf), cur_stream()))
+
+
+def train_steps_persistent(params: torch.Tensor, ws: Workspace, batch: int, nsteps: int, *,
+                           images: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor,
+                           masks: Optional[torch.Tensor] = None, philox: Optional[Tuple[int, int]] = None,
+                           grads: Optional[torch.Tensor] = None, grad_scale: float = 1.0, lr: float = 0.0,
+                           loss: Optional[torch.Tensor] = None, loss_steps: Optional[torch.Tensor] = None) -> None:
+    """`nsteps` whole optimisation steps in one cooperative launch (batch <= 512).
+    idx: i64[nsteps*batch] consecutive batches; masks: u8[nsteps,batch,128] or None."""
+    _need(params, "params", torch.float32, (N_PARAMS,))
+    if batch > ws.max_batch:
+        raise ValueError(f"batch {batch} exceeds workspace max_batch {ws.max_batch}")
+    _need(images, "images", torch.uint8)
+    n = images.shape[0]
+    _need(labels, "labels", torch.uint8, (n,))
+    _need(idx, "idx", torch.int64)
+    if idx.numel() < nsteps * batch:
+        raise ValueError("idx shorter than nsteps*batch")
+    _need(masks, "masks", torch.uint8, (nsteps, batch, HID), optional=True)
+    _need(grads, "grads", torch.float32, (N_PARAMS,), optional=True)
+    _need(loss, "loss", torch.float32, (2,), optional=True)
+    _need(loss_steps, "loss_steps", torch.float32, optional=True)
+    if loss_steps is not None and loss_steps.numel() < nsteps:
+        raise ValueError("loss_steps shorter than nsteps")
+    seed, step0 = philox if philox else (0, 0)
+    flags = _lib.FWD_PHILOX_MASK if philox else 0
+    check(lib.ddpm_train_steps_persistent(ptr(params), ptr(grads), ptr(images), ptr(labels), n, ptr(idx),
+                                          ptr(masks), seed, step0, batch, nsteps, flags, grad_scale, lr,
+                                          ptr(loss), ptr(loss_steps), ptr(ws.buf), cur_stream()))
 
 
 def cross_entropy(logits: torch.Tensor, y: torch.Tensor, loss: Optional[torch.Tensor] = None,

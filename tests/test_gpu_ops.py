@@ -302,3 +302,106 @@ def test_run_to_run_determinism(ops, dev, data, golden):
             ops.step_backward(params, ws, 64, images=images, idx=idx, lr=0.01)
         outs.append(params.clone())
     assert torch.equal(outs[0], outs[1])
+
+
+# ------------------------------------------------------------------------------ persistent kernel (v2)
+def test_persistent_step0_against_reference(ops, dev, data, golden):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    idx = torch.from_numpy(g["idx"][0]).to(dev)
+    p0 = _params(g, "params0")
+    params = _flat(p0, dev)
+    masks = torch.from_numpy(O.unpack_masks(g["masks"])[:1]).to(dev)
+    ws = ops.Workspace(64, dev)
+    loss = torch.zeros(2, device=dev)
+    grads = torch.zeros(O.N_PARAMS, device=dev)
+    # gradients only (lr = 0): parameters untouched
+    ops.train_steps_persistent(params, ws, 64, 1, images=images, labels=labels, idx=idx, masks=masks,
+                               grads=grads, loss=loss)
+    torch.cuda.synchronize()
+    assert torch.equal(params, _flat(p0, dev))
+    assert abs(float(loss[0]) - float(g["losses"][0])) < 1e-5
+    gu = O.unflatten_params(grads.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _rel(gu[k], g[f"grads0.{k}"]) < TOL_F32, k
+    # fused SGD: parameters after one step == reference's
+    ops.train_steps_persistent(params, ws, 64, 1, images=images, labels=labels, idx=idx, masks=masks, lr=0.01)
+    torch.cuda.synchronize()
+    pu = O.unflatten_params(params.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _rel(pu[k], g[f"params1.{k}"]) < 1e-6, k
+
+
+def test_persistent_trajectory_one_launch(ops, dev, data, golden):
+    """100 steps in ONE launch vs the reference's trajectory, and vs 100 single-step launches."""
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    masks = torch.from_numpy(O.unpack_masks(g["masks"])).to(dev)
+    idx = torch.from_numpy(g["idx"].reshape(-1)).to(dev)
+    ws = ops.Workspace(64, dev)
+    outs = []
+    for nper in (100, 1):
+        params = _flat(_params(g, "params0"), dev)
+        loss = torch.zeros(2, device=dev)
+        ls = torch.zeros(100, device=dev)
+        for s0 in range(0, 100, nper):
+            ops.train_steps_persistent(params, ws, 64, nper, images=images, labels=labels,
+                                       idx=idx[s0 * 64:(s0 + nper) * 64], masks=masks[s0:s0 + nper].contiguous(),
+                                       lr=0.01, loss=loss, loss_steps=ls[s0:s0 + nper])
+        torch.cuda.synchronize()
+        outs.append((params.clone(), ls.clone(), float(loss[1])))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    ln = outs[0][1].cpu().numpy()
+    assert np.abs(ln[:5] - g["losses"][:5]).max() < 1e-5
+    assert np.abs(ln - g["losses"]).max() < TOL_TRAJ * np.abs(g["losses"]).max()
+    pu = O.unflatten_params(outs[0][0].cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _fro(pu[k], g[f"paramsN.{k}"]) < TOL_TRAJ, k
+    assert abs(outs[0][2] - float(ln.astype(np.float64).sum() / 64)) < 1e-4
+
+
+@pytest.mark.parametrize("batch", [1, 12, 48, 65, 123, 124, 200, 512])
+def test_persistent_matches_oracle_all_batch_sizes(ops, dev, data, golden, batch):
+    g = golden["traj_ws1"]
+    images, labels, im, lb = data
+    rng = np.random.default_rng(2000 + batch)
+    idx_np = rng.integers(0, 60000, batch).astype(np.int64)
+    mask_np = (rng.random((batch, 128)) < 0.8).astype(np.uint8)
+    p = _params(g, "paramsN")
+    x, y = O.gather_decode(im, lb, idx_np)
+    p1, loss_ref, gr, _ = O.train_step(p, x, y, mask_np)
+    params = _flat(p, dev)
+    ws = ops.Workspace(batch, dev)
+    loss = torch.zeros(2, device=dev)
+    grads = torch.zeros(O.N_PARAMS, device=dev)
+    ops.train_steps_persistent(params, ws, batch, 1, images=images, labels=labels, idx=torch.from_numpy(idx_np).to(dev),
+                               masks=torch.from_numpy(mask_np[None]).to(dev), grads=grads, grad_scale=0.125, lr=0.01,
+                               loss=loss)
+    torch.cuda.synchronize()
+    assert abs(float(loss[0]) - float(loss_ref)) < 2e-5 * max(1.0, abs(float(loss_ref)))
+    gu = O.unflatten_params(grads.cpu().numpy())
+    for k in O.PARAM_KEYS:
+        assert _rel(gu[k], 0.125 * gr[k]) < 5e-5, k
+    # parameters moved by lr * (scaled gradient)
+    want = O.flatten_params(O.sgd_step(p, {k: (0.125 * v).astype(np.float32) for k, v in gr.items()}))
+    assert np.abs(params.cpu().numpy() - want).max() < 1e-6
+
+
+def test_persistent_philox_matches_three_kernel_path(ops, dev, data, golden):
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    idx = torch.from_numpy(g["idx"][:3].reshape(-1)).to(dev)
+    ws = ops.Workspace(64, dev)
+    pa = _flat(_params(g, "params0"), dev)
+    ops.train_steps_persistent(pa, ws, 64, 3, images=images, labels=labels, idx=idx, philox=(9, 40), lr=0.01)
+    pb = _flat(_params(g, "params0"), dev)
+    for t in range(3):
+        ops.step_forward(pb, ws, 64, images=images, labels=labels, idx=idx[t * 64:(t + 1) * 64], philox=(9, 40 + t),
+                         prep_backward=True)
+        ops.step_backward(pb, ws, 64, images=images, idx=idx[t * 64:(t + 1) * 64], lr=0.01)
+    torch.cuda.synchronize()
+    assert _rel(pa.cpu().numpy(), pb.cpu().numpy()) < 1e-5      # same masks, different summation order
+    from pytorch_ddp_mnist_b200._lib import DDPMError
+    with pytest.raises(DDPMError, match="outside"):
+        ops.train_steps_persistent(pa, ops.Workspace(600, dev), 600, 1, images=images, labels=labels,
+                                   idx=torch.zeros(600, dtype=torch.int64, device=dev), lr=0.01)
