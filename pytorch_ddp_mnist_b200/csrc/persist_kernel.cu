@@ -25,6 +25,10 @@
 
 #include "common.cuh"
 
+#ifndef DDPM_POLL_SLEEP
+#define DDPM_POLL_SLEEP 0
+#endif
+
 namespace ddpm {
 
 constexpr int P_THREADS = 256;
@@ -35,6 +39,7 @@ constexpr int N_W2T = 32;                             // dW2 tiles: 8 row tiles 
 constexpr int N_W3T = 4;                              // dW3 column tiles (32 cols); the same CTAs do db1, db2, loss
 constexpr int CTA_W2 = N_W1, CTA_W3 = N_W1 + N_W2T;
 constexpr int P_GRID = CTA_W3 + N_W3T;                // 148 = one CTA per SM
+constexpr int N_SMALL = N_W2T + N_W3T;                // 36 CTAs update W2, W3, b1, b2
 constexpr int CR = 64;                                // batch rows per smem chunk
 constexpr int XS_LD = 60;                             // padded row of the decoded pixel tile (16B aligned)
 constexpr int PERSIST_MAX_BATCH = 512;
@@ -47,12 +52,12 @@ struct PersistArgs {
     int B, nsteps; float gscale, lr; int train;
     float* loss2; float* loss_steps;
     float* part; float* h1d; float* h2; float* dz2; float* dz1; float* dz3; float* rowloss;
-    unsigned* bar;                                    // [0] arrival count, [1] generation
-    long long* dbg;                                   // optional [grid][8 steps][8] clock64 stamps (profiling aid)
+    unsigned long long* bar;                          // [0] monotonic arrival counter, [1] monotonic 'W2/W3/b ready' counter
+    long long* dbg;                                   // optional [grid][8 steps][16] clock64 stamps (profiling aid)
 };
 
 struct __align__(16) PersistSmem {
-    float w2[HID * HID];                              // swizzled at float4 granularity; reused as staging in phase C
+    float w2[HID * HID / 2];                          // 32 KB scratch: partial products (phase B), staging / partial gradients (phase C)
     float w3[NC * HID];
     float b1[HID], b2[HID];
     float w1t[NT * MT];                               // [n][m]  owned W1 tile (persistent across steps)
@@ -61,61 +66,79 @@ struct __align__(16) PersistSmem {
     float hs[HID], h2s[HID], ds[HID];                 // row vectors
     float red[2 * HID];
     float zs[NCP], dzs[NCP];
+    int ylab;
     float lut[256];
 };
 
-__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
-    unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ unsigned long long ld_acquire64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-
-// Sense-reversing grid barrier; all CTAs are co-resident (cooperative launch).  Arrival is one
-// acq_rel atomic (it publishes this CTA's writes: the bar.sync before it makes them visible to
-// thread 0, release is cumulative); the last arriver resets the count and bumps the generation
-// with a release store; waiters spin on an acquire load.
-__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& gen) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned arrived;
-        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(bar) : "memory");
-        if (arrived == gridDim.x - 1) {
-            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(bar), "r"(0u) : "memory");
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(bar + 1), "r"(gen + 1) : "memory");
-        } else {
-            while (ld_acquire(bar + 1) == gen) { }
-        }
-    }
-    gen += 1;
-    __syncthreads();
+__device__ __forceinline__ void red_release64(unsigned long long* p) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(p) : "memory");
 }
 
-__device__ __forceinline__ int w2_slot(int j, int q) { return j * 32 + (q ^ (j & 31)); }   // float4 index
+// Grid barrier on ONE monotonic 64-bit counter (all CTAs are co-resident: cooperative launch).
+// Arrive = one fire-and-forget release reduction (the bar.sync before it makes the CTA's writes
+// visible to thread 0; release is cumulative); wait = acquire-poll until the counter reaches this
+// barrier's target.  Every barrier adds exactly gridDim.x, so the value a CTA reads at kernel
+// start, rounded down to a multiple of gridDim.x, is the launch's base (at most gridDim.x-1
+// arrivals can precede its own): no reset, no second atomic, no host-side zeroing per launch.
+constexpr int BAR_TID = P_THREADS - 1;     // the barrier thread: it issues no global loads/stores of its own before
+                                           // arriving, so the release fence has nothing of its own to wait for
+__device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void grid_arrive(unsigned long long* ctr, unsigned long long& target) {
+    __syncthreads();
+    if (threadIdx.x == BAR_TID) { target += gridDim.x; red_release64(ctr); }
+}
+__device__ __forceinline__ void grid_wait(unsigned long long* ctr, const unsigned long long& target) {
+    // acquire-poll: measured 2461 cycles per barrier on B200 (148 CTAs) against 2823 for a relaxed poll
+    // followed by fence.acq_rel, 2420 for cooperative_groups grid.sync() and 1571 with no ordering at
+    // all (scripts/micro/barrier_bench.cu)
+    if (threadIdx.x == BAR_TID) { while (ld_acquire64(ctr) < target) { } }
+    __syncthreads();
+}
+__device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned long long& target) {
+    grid_arrive(ctr, target);
+    grid_wait(ctr, target);
+}
+
+__device__ __forceinline__ int w1_idx(int m, int n) { return (((n >> 2) * MT + m) << 2) + (n & 3); }   // [n/4][m][n%4]
 
 // Pixel tile [rows c0..c0+CR) x [56 pixels of tile nt]: loads first (all index loads, then all
 // pixel loads: two dependent round trips in total), LUT decode + store to smem later, so the
 // latency can sit behind a barrier wait.
 constexpr int PX_PER_ROW = NT / 4;                                         // 14 words of 4 pixels
 constexpr int PX_ITERS = (CR * PX_PER_ROW + P_THREADS - 1) / P_THREADS;    // 4
-struct PixelRegs { uint32_t v[PX_ITERS]; unsigned ok; };
+struct PixelRegs { int64_t sidx[PX_ITERS]; uint32_t v[PX_ITERS]; unsigned ok; };
 
-__device__ __forceinline__ void tile_load(PixelRegs& px, const PersistArgs& a, const int64_t* idx, int c0, int nt) {
-    int64_t sidx[PX_ITERS];
+__device__ __forceinline__ void tile_load_idx(PixelRegs& px, const PersistArgs& a, const int64_t* idx, int c0) {
 #pragma unroll
     for (int i = 0; i < PX_ITERS; ++i) {
         const int t = threadIdx.x + i * P_THREADS;
         const int row = c0 + t / PX_PER_ROW;
-        sidx[i] = (t < CR * PX_PER_ROW && row < a.B) ? __ldg(idx + row) : -1;
+        px.sidx[i] = (t < CR * PX_PER_ROW && row < a.B) ? __ldg(idx + row) : -1;
     }
+}
+__device__ __forceinline__ void tile_load_px(PixelRegs& px, const PersistArgs& a, int nt) {
     px.ok = 0;
 #pragma unroll
     for (int i = 0; i < PX_ITERS; ++i) {
         const int t = threadIdx.x + i * P_THREADS;
         const int q = t % PX_PER_ROW;
-        const bool ok = (sidx[i] >= 0 && sidx[i] < a.n_samples);
+        const bool ok = (px.sidx[i] >= 0 && px.sidx[i] < a.n_samples);
         px.ok |= (ok ? 1u : 0u) << i;
-        px.v[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(a.images + sidx[i] * IN + nt * NT) + q) : 0u;
+        px.v[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(a.images + px.sidx[i] * IN + nt * NT) + q) : 0u;
     }
+}
+__device__ __forceinline__ void tile_load(PixelRegs& px, const PersistArgs& a, const int64_t* idx, int c0, int nt) {
+    tile_load_idx(px, a, idx, c0);
+    tile_load_px(px, a, nt);
 }
 
 __device__ __forceinline__ void tile_store(const PixelRegs& px, PersistSmem& s, float* xs) {
@@ -134,6 +157,16 @@ __device__ __forceinline__ void tile_store(const PixelRegs& px, PersistSmem& s, 
     }
 }
 
+__device__ __forceinline__ void load_w2_block(float (&blk)[8][8], const float* W2, int jb, int kb) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const float4 v0 = __ldcg(reinterpret_cast<const float4*>(W2 + (size_t)(jb * 8 + r) * HID + kb * 8));
+        const float4 v1 = __ldcg(reinterpret_cast<const float4*>(W2 + (size_t)(jb * 8 + r) * HID + kb * 8) + 1);
+        blk[r][0] = v0.x; blk[r][1] = v0.y; blk[r][2] = v0.z; blk[r][3] = v0.w;
+        blk[r][4] = v1.x; blk[r][5] = v1.y; blk[r][6] = v1.z; blk[r][7] = v1.w;
+    }
+}
+
 __device__ __forceinline__ void grad_out(const PersistArgs& a, int off, float g, float pold) {
     if (a.grads) a.grads[off] = g;
     if (a.lr != 0.f) a.params[off] = fmaf(-a.lr, g, pold);
@@ -148,8 +181,10 @@ train_persist_kernel(PersistArgs a) {
     const int B = a.B;
     const float invB = 1.0f / (float)B;
     const float scale = a.train ? 1.25f : 1.0f;
-    unsigned gen = 0;
-    if (tid == 0) gen = ld_acquire(&a.bar[1]);        // only thread 0's copy is used by the barrier
+    unsigned long long bar_target = 0, ready_base = 0;     // used by BAR_TID / thread 0 only
+    if (tid == BAR_TID) bar_target = (ld_acquire64(&a.bar[0]) / gridDim.x) * gridDim.x;
+    if (tid == BAR_TID) ready_base = ld_acquire64(&a.bar[1]);   // nobody bumps it before the first barrier pair completes
+    unsigned long long ready_seen = 0;
     s.lut[tid] = decode_px(tid);
 
     const bool own_w1 = cta < N_W1;
@@ -161,8 +196,7 @@ train_persist_kernel(PersistArgs a) {
         for (int t = tid; t < MT * (NT / 4); t += P_THREADS) {
             const int m = t / (NT / 4), q = t - m * (NT / 4);
             const float4 v = *reinterpret_cast<const float4*>(a.params + DDPM_OFF_W1 + (size_t)(mt * MT + m) * IN + nt * NT + q * 4);
-            s.w1t[(q * 4 + 0) * MT + m] = v.x; s.w1t[(q * 4 + 1) * MT + m] = v.y;
-            s.w1t[(q * 4 + 2) * MT + m] = v.z; s.w1t[(q * 4 + 3) * MT + m] = v.w;
+            *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, q * 4)]) = v;
         }
         if (single) tile_load(px, a, a.idx, 0, nt);
     }
@@ -170,7 +204,13 @@ train_persist_kernel(PersistArgs a) {
     if (own_w1 && single) tile_store(px, s, s.xs[0]);
     __syncthreads();
 
-#define DBG_STAMP(slot) do { if (a.dbg && tid == 0 && step < 8) a.dbg[((size_t)cta * 8 + step) * 8 + (slot)] = clock64(); } while (0)
+// clock stamp that cannot be taken before a preceding bar.sync has actually released (BAR is
+// deferred-blocking: a bare clock read right after it reports the issue time): read a shared word first
+#define DBG_STAMP(slot) do { if (a.dbg && tid == 0 && step < 8) { \
+        unsigned v__; long long t__; \
+        asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v__) : "r"((unsigned)__cvta_generic_to_shared(&s.zs[0])) : "memory"); \
+        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t__) : "r"(v__) : "memory"); \
+        a.dbg[((size_t)cta * 8 + step) * 16 + (slot)] = t__; } } while (0)
     for (int step = 0; step < a.nsteps; ++step) {
         DBG_STAMP(0);
         const int64_t* idx = a.idx + (size_t)step * B;
@@ -181,6 +221,8 @@ train_persist_kernel(PersistArgs a) {
         // ================================ phase A ================================
         if (own_w1) {
             const int m = tid & 15, rg = tid >> 4;            // 16 row groups x 4 rows
+            if (prefetch) tile_load_idx(px, a, idx + B, 0);   // next step's sample indices: in flight during phase A
+            if (tid == BAR_TID && step > 0 && cta < B) ready_seen = ld_relaxed64(&a.bar[1]);
             __syncthreads();                                  // last step's in-place W1 tile update is complete
             for (int c = 0; c < nchunks; ++c) {
                 if (!single) {
@@ -192,14 +234,12 @@ train_persist_kernel(PersistArgs a) {
                 float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int n4 = 0; n4 < NT / 4; ++n4) {
-                    float w[4];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) w[i] = s.w1t[(n4 * 4 + i) * MT + m];
+                    const float4 w = *reinterpret_cast<const float4*>(&s.w1t[w1_idx(m, n4 * 4)]);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
                         const float4 x = *reinterpret_cast<const float4*>(&xs_cur[(rg * 4 + r) * XS_LD + n4 * 4]);
-                        acc[r] = fmaf(x.x, w[0], acc[r]); acc[r] = fmaf(x.y, w[1], acc[r]);
-                        acc[r] = fmaf(x.z, w[2], acc[r]); acc[r] = fmaf(x.w, w[3], acc[r]);
+                        acc[r] = fmaf(x.x, w.x, acc[r]); acc[r] = fmaf(x.y, w.y, acc[r]);
+                        acc[r] = fmaf(x.z, w.z, acc[r]); acc[r] = fmaf(x.w, w.w, acc[r]);
                     }
                 }
 #pragma unroll
@@ -210,33 +250,61 @@ train_persist_kernel(PersistArgs a) {
             }
             // next step's pixels do not depend on the weights: start fetching them now, decode
             // them after phase B; the two round trips hide behind the barrier waits
-            if (prefetch) tile_load(px, a, idx + B, 0, nt);
+            if (prefetch && tid != BAR_TID) tile_load_px(px, a, nt);
         }
         DBG_STAMP(1);
-        grid_barrier(a.bar, gen);
-        DBG_STAMP(2);
-
-        // ================================ phase B ================================
+        grid_arrive(a.bar, bar_target);
+        // While the barrier completes: fetch this step's W2 into REGISTERS — thread (jb, kb) keeps the
+        // 8x8 block W2[jb*8.., kb*8..], used by both the forward product (reduced over kb) and the
+        // backward product (reduced over jb) — and W3 / b1 / b2 into smem.  Their 36 owner CTAs bumped
+        // the 'ready' counter after last step's updates, long before this point.
+        float blk[8][8];
+        int yv_first = 0;
         if (cta < B) {
-            // stage W2 (swizzled), W3, b1, b2: they were updated by their owners in the last phase C
-            const float* W2 = a.params + DDPM_OFF_W2;
-            for (int t = tid; t < HID * HID / 4; t += P_THREADS) {
-                const int j = t >> 5, q = t & 31;
-                __pipeline_memcpy_async(&s.w2[w2_slot(j, q) * 4], W2 + (size_t)t * 4, 16);
+            if (step > 0) {
+                // normally satisfied by the sample taken at the start of phase A (the 36 owners finish early)
+                // (no fence: the owners released their updates before bumping the counter, and W2/W3/b are
+                //  read below with L2-coherent .cg loads that are issued only after this check succeeded)
+                if (tid == BAR_TID) {
+                    const unsigned long long need = ready_base + (unsigned long long)N_SMALL * step;
+                    while (ready_seen < need) ready_seen = ld_relaxed64(&a.bar[1]);
+                }
+                __syncthreads();
             }
+            if (tid != BAR_TID) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
             for (int t = tid; t < NC * HID / 4; t += P_THREADS)
                 __pipeline_memcpy_async(&s.w3[t * 4], a.params + DDPM_OFF_W3 + t * 4, 16);
             if (tid < HID / 4) __pipeline_memcpy_async(&s.b1[tid * 4], a.params + DDPM_OFF_B1 + tid * 4, 16);
             else if (tid < HID / 2) __pipeline_memcpy_async(&s.b2[(tid - HID / 4) * 4], a.params + DDPM_OFF_B2 + (tid - HID / 4) * 4, 16);
             __pipeline_commit();
+            if (tid == 32) {                                  // label of this CTA's first row: two dependent loads,
+                const int64_t sidx = __ldg(idx + cta);        // kept off the barrier thread and off warp 0
+                yv_first = (sidx >= 0 && sidx < a.n_samples) ? __ldg(a.labels + sidx) : 0;
+            }
+        }
+        grid_wait(a.bar, bar_target);
+        // the barrier thread kept its own memory pipeline empty while it was fencing; it catches up now
+        if (tid == BAR_TID) {
+            if (cta < B) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
+            if (prefetch) tile_load_px(px, a, nt);
+        }
+        DBG_STAMP(2);
+
+        // ================================ phase B ================================
+        if (cta < B) {
             const int j = tid & 127, h = tid >> 7;
+            const int jb = tid >> 4, kb = tid & 15;
+            float* red2 = s.w2;                               // [16][RLD] partial products (padded: conflict-free float4 stores)
+            constexpr int RLD = HID + 4;
             bool staged = false;
             for (int row = cta; row < B; row += gridDim.x) {
-                // label: two dependent loads, issued now, consumed in step 4
-                int yv = 0;
-                if (tid == 0) {
-                    const int64_t sidx = __ldg(idx + row);
-                    yv = (sidx >= 0 && sidx < a.n_samples) ? __ldg(a.labels + sidx) : 0;
+                if (tid == 32) {
+                    int yv = yv_first;
+                    if (row != cta) {
+                        const int64_t sidx = __ldg(idx + row);
+                        yv = (sidx >= 0 && sidx < a.n_samples) ? __ldg(a.labels + sidx) : 0;
+                    }
+                    s.ylab = yv;                              // read by warp 0 after three more barriers
                 }
                 // ---- 1. z1 = sum of the 14 tile partials (two fixed halves) + b1 ; ReLU ; dropout
                 float zp = 0.f;
@@ -256,6 +324,7 @@ train_persist_kernel(PersistArgs a) {
                 s.red[h * HID + j] = zp;
                 if (!staged) { __pipeline_wait_prior(0); staged = true; }
                 __syncthreads();
+                DBG_STAMP(6);
                 float h1 = 0.f;
                 if (h == 0) {
                     const float z = (s.red[j] + s.red[HID + j]) + s.b1[j];
@@ -264,39 +333,51 @@ train_persist_kernel(PersistArgs a) {
                     s.hs[j] = h1;
                 }
                 __syncthreads();
-                // ---- 2. z2 = h1d . W2^T + b2 (k range split over the two thread halves) ; ReLU
+                // ---- 2. z2 = h1d . W2^T + b2 : 8x8 block products, reduced over the 16 column blocks
                 {
-                    float a0 = 0.f, a1 = 0.f;
+                    const float4 x0 = *reinterpret_cast<const float4*>(&s.hs[kb * 8]);
+                    const float4 x1 = *reinterpret_cast<const float4*>(&s.hs[kb * 8 + 4]);
+                    const float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+                    float zr[8];
 #pragma unroll
-                    for (int qq = 0; qq < 16; qq += 2) {
-                        const int q0 = h * 16 + qq, q1 = q0 + 1;
-                        const float4 w0 = *reinterpret_cast<const float4*>(&s.w2[w2_slot(j, q0) * 4]);
-                        const float4 w1 = *reinterpret_cast<const float4*>(&s.w2[w2_slot(j, q1) * 4]);
-                        const float4 x0 = *reinterpret_cast<const float4*>(&s.hs[q0 * 4]);
-                        const float4 x1 = *reinterpret_cast<const float4*>(&s.hs[q1 * 4]);
-                        a0 = fmaf(x0.x, w0.x, a0); a0 = fmaf(x0.y, w0.y, a0); a0 = fmaf(x0.z, w0.z, a0); a0 = fmaf(x0.w, w0.w, a0);
-                        a1 = fmaf(x1.x, w1.x, a1); a1 = fmaf(x1.y, w1.y, a1); a1 = fmaf(x1.z, w1.z, a1); a1 = fmaf(x1.w, w1.w, a1);
+                    for (int r = 0; r < 8; ++r) {
+                        float v = 0.f;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) v = fmaf(blk[r][c], x[c], v);
+                        zr[r] = v;
                     }
-                    s.red[h * HID + j] = a0 + a1;
+                    *reinterpret_cast<float4*>(&red2[kb * RLD + jb * 8]) = make_float4(zr[0], zr[1], zr[2], zr[3]);
+                    *reinterpret_cast<float4*>(&red2[kb * RLD + jb * 8 + 4]) = make_float4(zr[4], zr[5], zr[6], zr[7]);
                 }
                 __syncthreads();
                 bool gate2 = false;
                 if (h == 0) {
-                    const float z2 = (s.red[j] + s.red[HID + j]) + s.b2[j];
+                    float z2 = 0.f;
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) z2 += red2[q * RLD + j];
+                    z2 += s.b2[j];
                     gate2 = z2 > 0.f;
                     const float hv = gate2 ? z2 : 0.f;
                     a.h2[(size_t)row * HID + j] = hv;
                     s.h2s[j] = hv;
                 }
                 __syncthreads();
-                // ---- 3. logits: class c handled by warp c (warps 0..7) and c+8 (warps 0..1)
-                for (int c = warp; c < NC; c += 8) {
-                    float v = 0.f;
+                DBG_STAMP(7);
+                // ---- 3. logits: warp w < 5 computes classes 2w and 2w+1 together (one pass, interleaved)
+                if (warp < NC / 2) {
+                    float v0 = 0.f, v1 = 0.f;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v = fmaf(s.h2s[lane + 32 * i], s.w3[c * HID + lane + 32 * i], v);
+                    for (int i = 0; i < 4; ++i) {
+                        const float hv = s.h2s[lane + 32 * i];
+                        v0 = fmaf(hv, s.w3[(2 * warp) * HID + lane + 32 * i], v0);
+                        v1 = fmaf(hv, s.w3[(2 * warp + 1) * HID + lane + 32 * i], v1);
+                    }
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                    if (lane == 0) s.zs[c] = v;
+                    for (int o = 16; o > 0; o >>= 1) {
+                        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+                        v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+                    }
+                    if (lane == 0) { s.zs[2 * warp] = v0; s.zs[2 * warp + 1] = v1; }
                 }
                 __syncthreads();
                 // ---- 4. log-softmax / NLL / dlogits by warp 0 (lane c < 10 holds class c)
@@ -304,12 +385,14 @@ train_persist_kernel(PersistArgs a) {
                     const float z = lane < NC ? s.zs[lane] : -INFINITY;
                     float m = z;
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                    for (int o = 8; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));   // classes live in lanes 0..9
                     const float e = lane < NC ? expf(z - m) : 0.f;
                     float sum = e;
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                    yv = __shfl_sync(0xffffffffu, yv, 0);
+                    for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    m = __shfl_sync(0xffffffffu, m, 0);
+                    sum = __shfl_sync(0xffffffffu, sum, 0);
+                    const int yv = s.ylab;
                     const float zy = __shfl_sync(0xffffffffu, z, yv);
                     if (lane == 0) a.rowloss[row] = -((zy - m) - logf(sum));
                     if (lane < NCP) {
@@ -319,6 +402,7 @@ train_persist_kernel(PersistArgs a) {
                     }
                 }
                 __syncthreads();
+                DBG_STAMP(8);
                 // ---- 5. dz2 = (dz3 . W3) * (z2 > 0)
                 if (h == 0) {
                     float d = 0.f;
@@ -329,24 +413,27 @@ train_persist_kernel(PersistArgs a) {
                     s.ds[j] = d;
                 }
                 __syncthreads();
-                // ---- 6. dz1 = (dz2 . W2) * scale * (kept && z1 > 0); j range split over the halves
+                // ---- 6. dz1 = (dz2 . W2) * scale * (kept && z1 > 0): same blocks, reduced over the 16 row blocks
                 {
-                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-                    const int kq = j >> 2, kr = j & 3;
+                    const float4 d0 = *reinterpret_cast<const float4*>(&s.ds[jb * 8]);
+                    const float4 d1 = *reinterpret_cast<const float4*>(&s.ds[jb * 8 + 4]);
+                    const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+                    float dc[8];
 #pragma unroll
-                    for (int jj = 0; jj < 64; jj += 4) {
-                        const int j0 = h * 64 + jj;
-                        const float4 d4 = *reinterpret_cast<const float4*>(&s.ds[j0]);
-                        a0 = fmaf(d4.x, s.w2[w2_slot(j0 + 0, kq) * 4 + kr], a0);
-                        a1 = fmaf(d4.y, s.w2[w2_slot(j0 + 1, kq) * 4 + kr], a1);
-                        a2 = fmaf(d4.z, s.w2[w2_slot(j0 + 2, kq) * 4 + kr], a2);
-                        a3 = fmaf(d4.w, s.w2[w2_slot(j0 + 3, kq) * 4 + kr], a3);
+                    for (int c = 0; c < 8; ++c) {
+                        float v = 0.f;
+#pragma unroll
+                        for (int r = 0; r < 8; ++r) v = fmaf(d[r], blk[r][c], v);
+                        dc[c] = v;
                     }
-                    s.red[h * HID + j] = (a0 + a1) + (a2 + a3);
+                    *reinterpret_cast<float4*>(&red2[jb * RLD + kb * 8]) = make_float4(dc[0], dc[1], dc[2], dc[3]);
+                    *reinterpret_cast<float4*>(&red2[jb * RLD + kb * 8 + 4]) = make_float4(dc[4], dc[5], dc[6], dc[7]);
                 }
                 __syncthreads();
                 if (h == 0) {
-                    const float v = s.red[j] + s.red[HID + j];
+                    float v = 0.f;
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) v += red2[q * RLD + j];
                     a.dz1[(size_t)row * HID + j] = (h1 > 0.f) ? v * scale : 0.f;
                 }
                 __syncthreads();
@@ -355,14 +442,20 @@ train_persist_kernel(PersistArgs a) {
         }
         if (prefetch) tile_store(px, s, s.xs[(step + 1) & 1]);    // the other buffer: phase C below still reads xs_cur
         DBG_STAMP(3);
-        grid_barrier(a.bar, gen);
+        grid_barrier(a.bar, bar_target);
         DBG_STAMP(4);
 
         // ================================ phase C ================================
         if (own_w1) {
-            const bool act = tid < MT * (NT / 4);               // 224 threads: (m, 4 pixels)
-            const int m = tid / (NT / 4), n4 = tid - m * (NT / 4);
-            float g[4] = {0.f, 0.f, 0.f, 0.f};
+            // thread -> (batch quarter qd, 4 units mq*4.., 4 pixels n4*4..): 16 FMAs per two LDS.128
+            const bool act = tid < 4 * 4 * (NT / 4);            // 224 threads
+            const int qd = tid / 56, u = tid - qd * 56, mq = u / (NT / 4), n4 = u - mq * (NT / 4);
+            float acc[4][4];
+            float db_acc = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int jx = 0; jx < 4; ++jx) acc[i][jx] = 0.f;
             for (int c = 0; c < nchunks; ++c) {
                 __syncthreads();
                 if (!single) { tile_load(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
@@ -373,37 +466,77 @@ train_persist_kernel(PersistArgs a) {
                     *reinterpret_cast<float4*>(&s.dzt[r * MT + q * 4]) = v;
                 }
                 __syncthreads();
+                DBG_STAMP(9);
+                if (nt == 0 && tid >= 224 && tid < 224 + MT) {        // db1 for this tile's 16 units (idle warp)
+                    const int m = tid - 224;
+                    float p[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int r = 0; r < CR; r += 4) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) p[i] += s.dzt[(r + i) * MT + m];
+                    }
+                    db_acc += (p[0] + p[1]) + (p[2] + p[3]);
+                }
                 if (act) {
-#pragma unroll 16
-                    for (int r = 0; r < CR; ++r) {
-                        const float d = s.dzt[r * MT + m];
+#pragma unroll
+                    for (int rr = 0; rr < CR / 4; ++rr) {
+                        const int r = qd * (CR / 4) + rr;
+                        const float4 d = *reinterpret_cast<const float4*>(&s.dzt[r * MT + mq * 4]);
                         const float4 x = *reinterpret_cast<const float4*>(&xs_cur[r * XS_LD + n4 * 4]);
-                        g[0] = fmaf(d, x.x, g[0]); g[1] = fmaf(d, x.y, g[1]);
-                        g[2] = fmaf(d, x.z, g[2]); g[3] = fmaf(d, x.w, g[3]);
+                        const float dv[4] = {d.x, d.y, d.z, d.w}, xv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int jx = 0; jx < 4; ++jx) acc[i][jx] = fmaf(dv[i], xv[jx], acc[i][jx]);
                     }
                 }
             }
+            if (nt == 0 && tid >= 224 && tid < 224 + MT) {
+                const int offb = DDPM_OFF_B1 + mt * MT + (tid - 224);
+                grad_out(a, offb, db_acc * a.gscale, __ldcg(a.params + offb));
+            }
+            float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
             if (act) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) g[i] *= a.gscale;
-                const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4 * 4;
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<float4*>(&pbuf[(qd * MT + mq * 4 + i) * NT + n4 * 4]) =
+                        make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            }
+            __syncthreads();
+            DBG_STAMP(10);
+            if (act) {
+                const int m = tid / (NT / 4), n4b = tid - m * (NT / 4);       // (unit, 4 pixels)
+                float4 p[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float4*>(&pbuf[(q * MT + m) * NT + n4b * 4]);
+                float g[4];
+                g[0] = ((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale;
+                g[1] = ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale;
+                g[2] = ((p[0].z + p[1].z) + (p[2].z + p[3].z)) * a.gscale;
+                g[3] = ((p[0].w + p[1].w) + (p[2].w + p[3].w)) * a.gscale;
+                const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
                 if (a.grads) *reinterpret_cast<float4*>(a.grads + off) = make_float4(g[0], g[1], g[2], g[3]);
                 if (a.lr != 0.f) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float& w = s.w1t[(n4 * 4 + i) * MT + m];
-                        w = fmaf(-a.lr, g[i], w);
-                    }
+                    float4 w = *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, n4b * 4)]);
+                    w.x = fmaf(-a.lr, g[0], w.x); w.y = fmaf(-a.lr, g[1], w.y);
+                    w.z = fmaf(-a.lr, g[2], w.z); w.w = fmaf(-a.lr, g[3], w.w);
+                    *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, n4b * 4)]) = w;
                 }
             }
         } else if (cta < CTA_W3) {
-            // ---- dW2 tile [16 rows jt][32 cols kt]; thread -> (row jj, columns 2*k2, 2*k2+1)
+            // ---- dW2 tile [16 rows jt][32 cols kt].  thread -> (batch quarter bq, 4 rows jq*4.., 2 cols k2*2..):
+            //      8 FMAs per LDS.128 + LDS.64; the four batch quarters are combined in fixed order.
             const int t2 = cta - CTA_W2, jt = t2 >> 2, kt = t2 & 3;
-            float* hst = s.w2;                                   // [CR][32] staging
-            const int jj = tid >> 4, k2 = tid & 15;
+            float* hst = s.w2;                                   // [CR][32] staging of h1d
+            float* pb = s.w2 + CR * 32;                          // [4][16][32] partial gradients
+            const int bq = tid >> 6, jq = (tid >> 4) & 3, k2 = tid & 15;
+            const int jj = tid >> 4;                             // final pass: (row jj, cols k2*2..)
             const int off = DDPM_OFF_W2 + (jt * 16 + jj) * HID + kt * 32 + k2 * 2;
             const float2 pold = __ldcg(reinterpret_cast<const float2*>(a.params + off));
-            float g0 = 0.f, g1 = 0.f;
+            const bool do_db = (kt == 0 && tid < 16);
+            const float pbias = do_db ? __ldcg(a.params + DDPM_OFF_B2 + jt * 16 + tid) : 0.f;
+            float acc[4][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
+            float db_acc = 0.f;
             for (int c = 0; c < nchunks; ++c) {
                 __syncthreads();
                 {
@@ -419,24 +552,55 @@ train_persist_kernel(PersistArgs a) {
                     *reinterpret_cast<float4*>(&hst[r * 32 + q * 4 + 16]) = u1;
                 }
                 __syncthreads();
-#pragma unroll 16
-                for (int r = 0; r < CR; ++r) {
-                    const float d = s.dzt[r * MT + jj];
+#pragma unroll
+                for (int rr = 0; rr < CR / 4; ++rr) {
+                    const int r = bq * (CR / 4) + rr;
+                    const float4 d = *reinterpret_cast<const float4*>(&s.dzt[r * MT + jq * 4]);
                     const float2 x = *reinterpret_cast<const float2*>(&hst[r * 32 + k2 * 2]);
-                    g0 = fmaf(d, x.x, g0); g1 = fmaf(d, x.y, g1);
+                    acc[0][0] = fmaf(d.x, x.x, acc[0][0]); acc[0][1] = fmaf(d.x, x.y, acc[0][1]);
+                    acc[1][0] = fmaf(d.y, x.x, acc[1][0]); acc[1][1] = fmaf(d.y, x.y, acc[1][1]);
+                    acc[2][0] = fmaf(d.z, x.x, acc[2][0]); acc[2][1] = fmaf(d.z, x.y, acc[2][1]);
+                    acc[3][0] = fmaf(d.w, x.x, acc[3][0]); acc[3][1] = fmaf(d.w, x.y, acc[3][1]);
+                }
+                if (do_db) {                                       // db2 for this tile's 16 units
+                    float p[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int r = 0; r < CR; r += 4) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) p[i] += s.dzt[(r + i) * MT + tid];
+                    }
+                    db_acc += (p[0] + p[1]) + (p[2] + p[3]);
                 }
             }
-            grad_out(a, off, g0 * a.gscale, pold.x);
-            grad_out(a, off + 1, g1 * a.gscale, pold.y);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                *reinterpret_cast<float2*>(&pb[(bq * 16 + jq * 4 + i) * 32 + k2 * 2]) = make_float2(acc[i][0], acc[i][1]);
+            __syncthreads();
+            {
+                float2 p[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
+                grad_out(a, off, ((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale, pold.x);
+                grad_out(a, off + 1, ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale, pold.y);
+            }
+            if (do_db) grad_out(a, DDPM_OFF_B2 + jt * 16 + tid, db_acc * a.gscale, pbias);
         } else {
-            // ---- dW3 column tile [10 classes][32 cols]; then db1 / db2 / loss on three of these CTAs
+            // ---- dW3 column tile [10 classes][32 cols].  thread -> (batch eighth bq, column k), all 10 classes:
+            //      10 FMAs per LDS + 3 broadcast LDS.128.  CTA kt == 2 also reduces the batch loss.
             const int kt = cta - CTA_W3;
             float* hst = s.w2;                                   // [CR][32] staging of h2
-            const int k = tid & 31, cg = tid >> 5;               // classes cg and cg + 8
-            const bool two = cg + 8 < NC;
-            const int off0 = DDPM_OFF_W3 + cg * HID + kt * 32 + k, off1 = off0 + 8 * HID;
-            const float p0 = __ldcg(a.params + off0), p1 = two ? __ldcg(a.params + off1) : 0.f;
-            float g0 = 0.f, g1 = 0.f;
+            float* pb = s.w2 + CR * 32;                          // [8][10][32] partial gradients
+            const int k = tid & 31, bq = tid >> 5;
+            const int c0 = tid >> 5, c1 = c0 + 8;                // final pass: classes c0 and (threads < 64) c1
+            const float p0 = __ldcg(a.params + DDPM_OFF_W3 + c0 * HID + kt * 32 + k);
+            const float p1 = c1 < NC ? __ldcg(a.params + DDPM_OFF_W3 + c1 * HID + kt * 32 + k) : 0.f;
+            float lsum = 0.f;
+            if (kt == 2) {                                       // per-row losses: loaded now, reduced at the end
+                for (int row = tid; row < B; row += P_THREADS) lsum += __ldcg(a.rowloss + row);
+            }
+            float acc[NC];
+#pragma unroll
+            for (int i = 0; i < NC; ++i) acc[i] = 0.f;
             for (int c = 0; c < nchunks; ++c) {
                 __syncthreads();
                 {
@@ -452,67 +616,51 @@ train_persist_kernel(PersistArgs a) {
                     *reinterpret_cast<float4*>(&hst[r * 32 + q * 4 + 16]) = u1;
                 }
                 __syncthreads();
-#pragma unroll 16
-                for (int r = 0; r < CR; ++r) {
+#pragma unroll
+                for (int rr = 0; rr < CR / 8; ++rr) {
+                    const int r = bq * (CR / 8) + rr;
                     const float hv = hst[r * 32 + k];
-                    g0 = fmaf(s.dzt[r * MT + cg], hv, g0);
-                    if (two) g1 = fmaf(s.dzt[r * MT + cg + 8], hv, g1);
+                    const float4 d0 = *reinterpret_cast<const float4*>(&s.dzt[r * MT]);
+                    const float4 d1 = *reinterpret_cast<const float4*>(&s.dzt[r * MT + 4]);
+                    const float2 d2 = *reinterpret_cast<const float2*>(&s.dzt[r * MT + 8]);
+                    acc[0] = fmaf(d0.x, hv, acc[0]); acc[1] = fmaf(d0.y, hv, acc[1]); acc[2] = fmaf(d0.z, hv, acc[2]);
+                    acc[3] = fmaf(d0.w, hv, acc[3]); acc[4] = fmaf(d1.x, hv, acc[4]); acc[5] = fmaf(d1.y, hv, acc[5]);
+                    acc[6] = fmaf(d1.z, hv, acc[6]); acc[7] = fmaf(d1.w, hv, acc[7]); acc[8] = fmaf(d2.x, hv, acc[8]);
+                    acc[9] = fmaf(d2.y, hv, acc[9]);
                 }
             }
-            grad_out(a, off0, g0 * a.gscale, p0);
-            if (two) grad_out(a, off1, g1 * a.gscale, p1);
-            if (kt < 2) {
-                // ---- db1 (kt 0) / db2 (kt 1): stage the [rows][128] block, column sums in fixed order
-                const float* D = kt == 0 ? a.dz1 : a.dz2;
-                const int col = tid & 127, half = tid >> 7;
-                const int offb = (kt == 0 ? DDPM_OFF_B1 : DDPM_OFF_B2) + col;
-                const float pb = __ldcg(a.params + offb);
-                float acc = 0.f;
-                float* st = s.w2;                                // [CR][128]
-                for (int c = 0; c < nchunks; ++c) {
-                    __syncthreads();
-                    float4 v[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int t = tid + i * P_THREADS, r = t >> 5, q = t & 31, row = c * CR + r;
-                        v[i] = row < B ? __ldcg(reinterpret_cast<const float4*>(D + (size_t)row * HID) + q)
-                                       : make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
+            for (int i = 0; i < NC; ++i) pb[(bq * NC + i) * 32 + k] = acc[i];
+            if (kt == 2) s.red[tid] = lsum;
+            __syncthreads();
+            {
+                float g0 = 0.f, g1 = 0.f;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int t = tid + i * P_THREADS;
-                        *reinterpret_cast<float4*>(&st[t * 4]) = v[i];
-                    }
-                    __syncthreads();
-                    float p[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
+                grad_out(a, DDPM_OFF_W3 + c0 * HID + kt * 32 + k, g0 * a.gscale, p0);
+                if (c1 < NC) {
 #pragma unroll
-                    for (int r = 0; r < CR / 2; r += 4) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) p[i] += st[(half * (CR / 2) + r + i) * HID + col];
-                    }
-                    acc += (p[0] + p[1]) + (p[2] + p[3]);
+                    for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
+                    grad_out(a, DDPM_OFF_W3 + c1 * HID + kt * 32 + k, g1 * a.gscale, p1);
                 }
-                __syncthreads();
-                s.red[half * HID + col] = acc;
-                __syncthreads();
-                if (half == 0) grad_out(a, offb, (s.red[col] + s.red[HID + col]) * a.gscale, pb);
-            } else if (kt == 2) {
-                // ---- batch loss: fixed-order sum of the per-row losses
+            }
+            if (kt == 2 && warp == 0) {
+                // batch loss: 256 strided partial sums -> 32 lanes (fixed order) -> shuffle tree
                 float v = 0.f;
-                for (int row = tid; row < B; row += P_THREADS) v += __ldcg(a.rowloss + row);
-                __syncthreads();
-                s.red[tid] = v;
-                __syncthreads();
-                for (int o = P_THREADS / 2; o > 0; o >>= 1) {
-                    if (tid < o) s.red[tid] += s.red[tid + o];
-                    __syncthreads();
-                }
-                if (tid == 0) {
-                    const float mean = s.red[0] * invB;
+#pragma unroll
+                for (int q = 0; q < P_THREADS / 32; ++q) v += s.red[q * 32 + lane];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) {
+                    const float mean = v * invB;
                     if (a.loss_steps) a.loss_steps[step] = mean;
                     if (a.loss2) { a.loss2[0] = mean; a.loss2[1] += mean * invB; }
                 }
             }
+        }
+        if (!own_w1 && a.lr != 0.f) {                         // W2 / W3 / b1 / b2 of the next step are in place
+            __syncthreads();
+            if (tid == 0) red_release64(&a.bar[1]);
         }
         DBG_STAMP(5);
         // no barrier here: W1 tiles are private; everything else is ordered by the next step's
@@ -524,9 +672,7 @@ train_persist_kernel(PersistArgs a) {
         __syncthreads();
         for (int t = tid; t < MT * (NT / 4); t += P_THREADS) {
             const int m = t / (NT / 4), q = t - m * (NT / 4);
-            float4 v;
-            v.x = s.w1t[(q * 4 + 0) * MT + m]; v.y = s.w1t[(q * 4 + 1) * MT + m];
-            v.z = s.w1t[(q * 4 + 2) * MT + m]; v.w = s.w1t[(q * 4 + 3) * MT + m];
+            const float4 v = *reinterpret_cast<const float4*>(&s.w1t[w1_idx(m, q * 4)]);
             *reinterpret_cast<float4*>(a.params + DDPM_OFF_W1 + (size_t)(mt * MT + m) * IN + nt * NT + q * 4) = v;
         }
     }
@@ -588,7 +734,7 @@ extern "C" int ddpm_train_steps_persistent(
     a.h1d = (float*)(ws + L.h1d); a.h2 = (float*)(ws + L.h2);
     a.dz2 = (float*)(ws + L.dz2); a.dz1 = (float*)(ws + L.dz1);
     a.dz3 = (float*)(ws + L.dz3); a.rowloss = (float*)(ws + L.rowloss);
-    a.bar = (unsigned*)(ws + L.ctrl) + 2;
+    a.bar = (unsigned long long*)(ws + L.ctrl) + 2;     // ctrl words 4..7
     a.dbg = g_persist_dbg;
     void* kargs[] = {&a};
     DDPM_CUDA(cudaLaunchCooperativeKernel((const void*)train_persist_kernel, dim3(P_GRID), dim3(P_THREADS), kargs,
