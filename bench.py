@@ -120,7 +120,9 @@ def _config(args, extra=None):
          "l2": "resident u8 dataset is 188 MB (> 126 MB L2) and every step gathers rows not touched before; "
                "weights stay L2-resident as in any training loop",
          "steps_per_launch_or_graph": CHUNK,
-         "step_kernel": "three-kernel (v1)" if args.three_kernel or args.batch > 512 else "persistent (v2)"}
+         "step_kernel": "three-kernel (v1)" if args.three_kernel or args.batch > 512 else "persistent (v2)",
+         "gradient_exchange": "NCCL allreduce between kernels" if args.no_fused else
+                              "in-kernel over NVLink peer memory (pull, fixed rank order), ws > 1 only"}
     if extra:
         c.update(extra)
     return c
@@ -135,6 +137,7 @@ def main() -> None:
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fused", action="store_true", help="ws > 1: NCCL allreduce between kernels instead of the fused peer-memory exchange")
     ap.add_argument("--three-kernel", action="store_true", help="use the v1 three-kernel step instead of the persistent kernel")
     ap.add_argument("--cpu-baseline-steps", type=int, default=150)
     args = ap.parse_args()
@@ -191,10 +194,13 @@ def main() -> None:
             eng.train_steps(resident, batches[t % chunk], B, 1)
         else:
             eng.train_step(resident, batches[t % chunk])
-    use_graph = (world > 1) or not persistent
+    fused = persistent and world > 1 and not args.no_fused
+    if fused:
+        eng.enable_fused_ddp()                              # gradient exchange inside the kernel (NVLink peer memory)
+    use_graph = ((world > 1) and not fused) or not persistent
     graph = eng.capture_steps(resident, batches, persistent=persistent) if use_graph else None
     if persistent:
-        kernels_per_chunk = 1 if world == 1 else 2 * chunk   # persistent (+ sgd per step); NCCL's kernel not counted
+        kernels_per_chunk = 1 if (world == 1 or fused) else 2 * chunk   # persistent (+ sgd per step); NCCL's kernel not counted
     else:
         kernels_per_chunk = (3 if world == 1 else 4) * chunk
 
@@ -217,7 +223,7 @@ def main() -> None:
             else:
                 eng.train_step(resident, shard_dev[s:s + B])
             done += 1
-            launches += kernels_per_chunk // chunk if (world > 1 or not persistent) else 1
+            launches += kernels_per_chunk // chunk if use_graph else 1
         return launches
 
     run(W, 0)

@@ -9,7 +9,8 @@
  * Conventions
  *   - plain C types only; every pointer named d_* is a DEVICE pointer owned by the caller
  *     (PyTorch tensors in practice), h_* is a HOST pointer.  The library allocates no device
- *     memory and keeps no pointer after a call returns.
+ *     memory and keeps no pointer after a call returns (one exception: the ddpm_comm_* communicator
+ *     of the fused data-parallel step owns one small symmetric buffer).
  *   - every GPU entry point is asynchronous and ordered on `stream` (a cudaStream_t passed as
  *     void*; NULL = legacy default stream); none of them synchronises or allocates, so they can be
  *     captured in a CUDA graph.
@@ -135,6 +136,41 @@ int ddpm_train_steps_persistent(float* d_params, float* d_grads,
                                 uint64_t philox_seed, uint64_t philox_step0,
                                 int batch, int nsteps, unsigned flags, float grad_scale, float lr,
                                 float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);
+
+/* -------------------------------------------------------------------------------- fused data-parallel step
+ * DistributedDataParallel's gradient averaging (mp:439: one 473,088-byte bucket, pre-divided by
+ * world_size, summed over ranks) + optimizer.step() (mp:463), done INSIDE the persistent step
+ * kernel over NVLink peer memory with a low-latency "flag in the data" protocol: the thread that
+ * produced a gradient element stores it as an 8-byte (value, step) word straight into every peer's
+ * receive buffer, then polls the same element of every source in its own buffer, sums in rank order
+ * (bit-identical replicas) and applies the SGD update in place.  No fences, no collective library
+ * call and no kernel launch between steps.
+ *
+ * A communicator owns one symmetric device buffer (1.9 MB per rank of the job, the only device memory this library
+ * allocates) that every peer process maps with CUDA IPC.  One process per GPU, all GPUs in one
+ * NVLink/P2P domain, world <= 8.  Set-up (host side, blocking):
+ *   ddpm_comm_create(rank, world, &c)            on every rank (its GPU current)
+ *   ddpm_comm_ipc_handle(c, handle64)            64-byte handle of the local buffer
+ *   -- exchange the handles (e.g. torch.distributed.all_gather_object) --
+ *   ddpm_comm_connect(c, handles[world][64])     maps every peer's buffer
+ * Every rank must then call ddpm_train_steps_fused_ddp with the same batch-independent arguments
+ * (nsteps, lr) in the same order.  A peer that never shows up makes the waiting kernels time out
+ * after ~3 s and set an error word readable with ddpm_comm_error (no GPU hang). */
+typedef struct ddpm_comm ddpm_comm;
+int  ddpm_comm_create(int rank, int world, ddpm_comm** out);
+int  ddpm_comm_ipc_handle(const ddpm_comm* c, void* h_out64);
+int  ddpm_comm_connect(ddpm_comm* c, const void* h_handles);
+int  ddpm_comm_error(const ddpm_comm* c, int* h_err);
+void ddpm_comm_destroy(ddpm_comm* c);
+/* Same arguments as ddpm_train_steps_persistent minus d_grads/grad_scale (the bucket is the
+ * communicator's; gradients are scaled by 1/world).  d_loss reports THIS rank's batch loss, as the
+ * reference's per-rank `batch_loss` does (mp:461). */
+int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,
+                               const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                               const int64_t* d_idx, const uint8_t* d_masks,
+                               uint64_t philox_seed, uint64_t philox_step0,
+                               int batch, int nsteps, unsigned flags, float lr,
+                               float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);
 
 /* Forward/eval step for callers that cannot allocate.  No counterpart in the reference (added for
  * embedding; the reference is a script that allocates freely through torch).

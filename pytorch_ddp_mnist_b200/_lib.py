@@ -52,6 +52,13 @@ SIGNATURES = {
                                                 _u32, _vp, _vp, _vp]),
     "ddpm_train_steps_persistent": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32,
                                            _f32, _f32, _vp, _vp, _vp, _vp]),
+    "ddpm_comm_create": (_i32, [_i32, _i32, C.POINTER(_vp)]),
+    "ddpm_comm_ipc_handle": (_i32, [_vp, _vp]),
+    "ddpm_comm_connect": (_i32, [_vp, _vp]),
+    "ddpm_comm_error": (_i32, [_vp, C.POINTER(_i32)]),
+    "ddpm_comm_destroy": (None, [_vp]),
+    "ddpm_train_steps_fused_ddp": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32, _f32,
+                                          _vp, _vp, _vp, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),

@@ -43,6 +43,7 @@ constexpr int N_SMALL = N_W2T + N_W3T;                // 36 CTAs update W2, W3, 
 constexpr int CR = 64;                                // batch rows per smem chunk
 constexpr int XS_LD = 60;                             // padded row of the decoded pixel tile (16B aligned)
 constexpr int PERSIST_MAX_BATCH = 512;
+#define DDPM_MAX_WORLD 8
 
 struct PersistArgs {
     float* params; float* grads;
@@ -54,6 +55,12 @@ struct PersistArgs {
     float* part; float* h1d; float* h2; float* dz2; float* dz1; float* dz3; float* rowloss;
     unsigned long long* bar;                          // [0] monotonic arrival counter, [1] monotonic 'W2/W3/b ready' counter
     long long* dbg;                                   // optional [grid][8 steps][16] clock64 stamps (profiling aid)
+    // ---- fused data-parallel mode (world > 1): gradient tiles are exchanged over NVLink peer memory
+    int world, rank;
+    unsigned long long comm_step;                     // number of fused steps this communicator ran before this launch
+    unsigned long long* xrecv[DDPM_MAX_WORLD];        // every rank's receive buffer [2 parities][world sources][NP] of
+                                                      // 8-byte (value, step) words, peer-mapped
+    int* xerr;                                        // local error word (exchange timeout)
 };
 
 struct __align__(16) PersistSmem {
@@ -167,9 +174,77 @@ __device__ __forceinline__ void load_w2_block(float (&blk)[8][8], const float* W
     }
 }
 
-__device__ __forceinline__ void grad_out(const PersistArgs& a, int off, float g, float pold) {
-    if (a.grads) a.grads[off] = g;
-    if (a.lr != 0.f) a.params[off] = fmaf(-a.lr, g, pold);
+// gout/lr are the per-step destinations: the caller's d_grads and a.lr normally; in fused
+// data-parallel mode the local exchange bucket and 0 (the update happens after the exchange).
+__device__ __forceinline__ void grad_out(float* gout, float lr, float* params, int off, float g, float pold) {
+    if (gout) gout[off] = g;
+    if (lr != 0.f) params[off] = fmaf(-lr, g, pold);
+}
+
+// ---- fused data-parallel exchange: low-latency "flag in the data" protocol over NVLink peer memory.
+// Every gradient value travels as one 8-byte word (fp32 value, 32-bit step number) stored straight
+// into the receive buffer of each peer; 8-byte stores are single transactions, so a word whose
+// step field equals T carries step T's value.  No fences, no separate flags, no barrier: the thread
+// that produced an element sends it and later polls the same element of every source in its own
+// (local) receive buffer, summing in rank order — identical on all ranks, hence bit-identical
+// replicas.  Slots are double-buffered by step parity: a rank can only be one step ahead of a peer.
+template <int N>
+__device__ __forceinline__ void ll_send(const PersistArgs& a, unsigned long long T, int off, const float (&v)[N]) {
+    const unsigned t32 = (unsigned)T;
+    const size_t slot = ((size_t)(T & 1) * a.world + a.rank) * NP + off;
+    for (int r = 0; r < a.world; ++r) {
+        if (r == a.rank) continue;
+        unsigned long long* dst = a.xrecv[r] + slot;
+        if (N == 1) {
+            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"(__float_as_uint(v[0])), "r"(t32) : "memory");
+        } else {
+#pragma unroll
+            for (int i = 0; i < N; i += 2)
+                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst + i), "r"(__float_as_uint(v[i])),
+                             "r"(t32), "r"(__float_as_uint(v[i + (N > 1 ? 1 : 0)])), "r"(t32) : "memory");
+        }
+    }
+}
+// v holds this rank's own contribution on entry and the sum over all ranks (rank order) on exit.
+template <int N>
+__device__ __forceinline__ void ll_reduce(const PersistArgs& a, unsigned long long T, int off, float (&v)[N]) {
+    const unsigned t32 = (unsigned)T;
+    float own[N], sum[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) { own[i] = v[i]; sum[i] = 0.f; }
+    const long long t0 = clock64();
+    for (int r = 0; r < a.world; ++r) {
+        float got[N];
+        if (r == a.rank) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) got[i] = own[i];
+        } else {
+            const unsigned long long* src = a.xrecv[a.rank] + ((size_t)(T & 1) * a.world + r) * NP + off;
+            if (N == 1) {
+                unsigned x, f;
+                do {
+                    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
+                    if (f != t32 && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }      // ~3 s: peer missing
+                } while (f != t32);
+                got[0] = __uint_as_float(x);
+            } else {
+#pragma unroll
+                for (int i = 0; i < N; i += 2) {
+                    unsigned x0, f0, x1, f1;
+                    do {
+                        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(f0), "=r"(x1), "=r"(f1)
+                                     : "l"(src + i) : "memory");
+                        if ((f0 != t32 || f1 != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
+                    } while (f0 != t32 || f1 != t32);
+                    got[i] = __uint_as_float(x0); got[i + (N > 1 ? 1 : 0)] = __uint_as_float(x1);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < N; ++i) sum[i] = (r == 0) ? got[i] : sum[i] + got[i];
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = sum[i];
 }
 
 __global__ void __launch_bounds__(P_THREADS, 1)
@@ -217,6 +292,8 @@ train_persist_kernel(PersistArgs a) {
         const uint8_t* mask = a.masks ? a.masks + (size_t)step * B * HID : nullptr;
         float* xs_cur = s.xs[step & 1];
         const bool prefetch = own_w1 && single && (step + 1 < a.nsteps);
+        const bool ddp = a.world > 1;
+        const unsigned long long T = a.comm_step + step + 1;            // global step number of this communicator
 
         // ================================ phase A ================================
         if (own_w1) {
@@ -493,7 +570,10 @@ train_persist_kernel(PersistArgs a) {
             }
             if (nt == 0 && tid >= 224 && tid < 224 + MT) {
                 const int offb = DDPM_OFF_B1 + mt * MT + (tid - 224);
-                grad_out(a, offb, db_acc * a.gscale, __ldcg(a.params + offb));
+                float gb[1] = {db_acc * a.gscale};
+                const float pold = __ldcg(a.params + offb);
+                if (ddp) { ll_send<1>(a, T, offb, gb); ll_reduce<1>(a, T, offb, gb); }
+                grad_out(a.grads, a.lr, a.params, offb, gb[0], pold);
             }
             float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
             if (act) {
@@ -515,6 +595,12 @@ train_persist_kernel(PersistArgs a) {
                 g[2] = ((p[0].z + p[1].z) + (p[2].z + p[3].z)) * a.gscale;
                 g[3] = ((p[0].w + p[1].w) + (p[2].w + p[3].w)) * a.gscale;
                 const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
+                if (ddp) {                                      // push to every peer, then sum everyone's tile
+                    ll_send<4>(a, T, off, g);
+                    DBG_STAMP(11);
+                    ll_reduce<4>(a, T, off, g);
+                    DBG_STAMP(12);
+                }
                 if (a.grads) *reinterpret_cast<float4*>(a.grads + off) = make_float4(g[0], g[1], g[2], g[3]);
                 if (a.lr != 0.f) {
                     float4 w = *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, n4b * 4)]);
@@ -580,10 +666,18 @@ train_persist_kernel(PersistArgs a) {
                 float2 p[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
-                grad_out(a, off, ((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale, pold.x);
-                grad_out(a, off + 1, ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale, pold.y);
+                float g[2] = {((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale,
+                              ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale};
+                if (ddp) { ll_send<2>(a, T, off, g); ll_reduce<2>(a, T, off, g); }
+                grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
+                grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
             }
-            if (do_db) grad_out(a, DDPM_OFF_B2 + jt * 16 + tid, db_acc * a.gscale, pbias);
+            if (do_db) {
+                const int offb = DDPM_OFF_B2 + jt * 16 + tid;
+                float gb[1] = {db_acc * a.gscale};
+                if (ddp) { ll_send<1>(a, T, offb, gb); ll_reduce<1>(a, T, offb, gb); }
+                grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
+            }
         } else {
             // ---- dW3 column tile [10 classes][32 cols].  thread -> (batch eighth bq, column k), all 10 classes:
             //      10 FMAs per LDS + 3 broadcast LDS.128.  CTA kt == 2 also reduces the batch loss.
@@ -637,11 +731,16 @@ train_persist_kernel(PersistArgs a) {
                 float g0 = 0.f, g1 = 0.f;
 #pragma unroll
                 for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
-                grad_out(a, DDPM_OFF_W3 + c0 * HID + kt * 32 + k, g0 * a.gscale, p0);
+                const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
+                float ga[1] = {g0 * a.gscale};
+                if (ddp) { ll_send<1>(a, T, o0, ga); ll_reduce<1>(a, T, o0, ga); }
+                grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) {
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
-                    grad_out(a, DDPM_OFF_W3 + c1 * HID + kt * 32 + k, g1 * a.gscale, p1);
+                    float gc[1] = {g1 * a.gscale};
+                    if (ddp) { ll_send<1>(a, T, o1, gc); ll_reduce<1>(a, T, o1, gc); }
+                    grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
                 }
             }
             if (kt == 2 && warp == 0) {
@@ -686,26 +785,10 @@ static long long* g_persist_dbg = nullptr;
 // profiling aid (not part of the public header): clock64 stamps of the first 8 steps of each CTA
 extern "C" void ddpm_debug_set_persist_timing(long long* d_buf) { g_persist_dbg = d_buf; }
 
-extern "C" int ddpm_train_steps_persistent(
-        float* d_params, float* d_grads,
-        const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
-        const int64_t* d_idx, const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
-        int batch, int nsteps, unsigned flags, float grad_scale, float lr,
-        float* d_loss, float* d_loss_steps, void* d_workspace, void* stream) {
-    DDPM_CHECK_ARG(batch > 0 && batch <= PERSIST_MAX_BATCH,
-                   "ddpm_train_steps_persistent: batch %d outside [1, %d] (use ddpm_step_forward/backward for larger batches)",
-                   batch, PERSIST_MAX_BATCH);
-    DDPM_CHECK_ARG(nsteps > 0, "ddpm_train_steps_persistent: nsteps must be positive (got %d)", nsteps);
-    DDPM_CHECK_ARG(d_params && d_images && d_labels && d_idx && d_workspace && n_samples > 0,
-                   "ddpm_train_steps_persistent: null pointer or empty dataset");
-    DDPM_CHECK_ARG((flags & ~DDPM_FWD_PHILOX_MASK) == 0, "ddpm_train_steps_persistent: unknown flags %#x", flags);
-    DDPM_CHECK_ARG(d_grads == nullptr || nsteps == 1 || lr != 0.f,
-                   "ddpm_train_steps_persistent: with lr == 0 only one step per launch makes sense");
-    DDPM_CHECK_ARG(d_grads != nullptr || lr != 0.f, "ddpm_train_steps_persistent: nothing to do (no d_grads and lr == 0)");
-    DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0 && ((uintptr_t)d_params & 15) == 0 &&
-                   ((uintptr_t)d_grads & 15) == 0 && ((uintptr_t)d_images & 3) == 0,
-                   "ddpm_train_steps_persistent: misaligned pointer");
-    cudaStream_t st = (cudaStream_t)stream;
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+static int persist_configure() {
     static bool configured[64] = {};
     int dev = 0;
     DDPM_CUDA(cudaGetDevice(&dev));
@@ -715,13 +798,30 @@ extern "C" int ddpm_train_steps_persistent(
         int per_sm = 0, sms = 0;
         DDPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, train_persist_kernel, P_THREADS, smem));
         DDPM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        DDPM_CHECK_ARG(per_sm * sms >= P_GRID, "ddpm_train_steps_persistent: device cannot co-schedule %d blocks", P_GRID);
+        DDPM_CHECK_ARG(per_sm * sms >= P_GRID, "persistent kernel: device cannot co-schedule %d blocks", P_GRID);
         configured[dev] = true;
     }
+    return 0;
+}
+
+static int persist_fill_and_launch(PersistArgs& a, float* d_params, float* d_grads,
+                                   const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                                   const int64_t* d_idx, const uint8_t* d_masks, uint64_t philox_seed,
+                                   uint64_t philox_step0, int batch, int nsteps, unsigned flags, float grad_scale,
+                                   float lr, float* d_loss, float* d_loss_steps, void* d_workspace, void* stream,
+                                   const char* who) {
+    DDPM_CHECK_ARG(batch > 0 && batch <= PERSIST_MAX_BATCH,
+                   "%s: batch %d outside [1, %d] (use ddpm_step_forward/backward for larger batches)", who, batch,
+                   PERSIST_MAX_BATCH);
+    DDPM_CHECK_ARG(nsteps > 0, "%s: nsteps must be positive (got %d)", who, nsteps);
+    DDPM_CHECK_ARG(d_params && d_images && d_labels && d_idx && d_workspace && n_samples > 0,
+                   "%s: null pointer or empty dataset", who);
+    DDPM_CHECK_ARG((flags & ~DDPM_FWD_PHILOX_MASK) == 0, "%s: unknown flags %#x", who, flags);
+    DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0 && ((uintptr_t)d_params & 15) == 0 &&
+                   ((uintptr_t)d_grads & 15) == 0 && ((uintptr_t)d_images & 3) == 0, "%s: misaligned pointer", who);
+    if (persist_configure()) return 1;
     char* ws = (char*)d_workspace;
     const WsLayout L = ws_layout(batch);
-    PersistArgs a;
-    memset(&a, 0, sizeof(a));
     a.params = d_params; a.grads = d_grads;
     a.images = d_images; a.labels = d_labels; a.n_samples = n_samples;
     a.idx = d_idx;
@@ -738,6 +838,112 @@ extern "C" int ddpm_train_steps_persistent(
     a.dbg = g_persist_dbg;
     void* kargs[] = {&a};
     DDPM_CUDA(cudaLaunchCooperativeKernel((const void*)train_persist_kernel, dim3(P_GRID), dim3(P_THREADS), kargs,
-                                          (size_t)smem, st));
+                                          sizeof(PersistSmem), (cudaStream_t)stream));
     return 0;
+}
+
+extern "C" int ddpm_train_steps_persistent(
+        float* d_params, float* d_grads,
+        const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+        const int64_t* d_idx, const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
+        int batch, int nsteps, unsigned flags, float grad_scale, float lr,
+        float* d_loss, float* d_loss_steps, void* d_workspace, void* stream) {
+    DDPM_CHECK_ARG(d_grads == nullptr || nsteps == 1 || lr != 0.f,
+                   "ddpm_train_steps_persistent: with lr == 0 only one step per launch makes sense");
+    DDPM_CHECK_ARG(d_grads != nullptr || lr != 0.f, "ddpm_train_steps_persistent: nothing to do (no d_grads and lr == 0)");
+    PersistArgs a;
+    memset(&a, 0, sizeof(a));
+    a.world = 1;
+    return persist_fill_and_launch(a, d_params, d_grads, d_images, d_labels, n_samples, d_idx, d_masks, philox_seed,
+                                   philox_step0, batch, nsteps, flags, grad_scale, lr, d_loss, d_loss_steps,
+                                   d_workspace, stream, "ddpm_train_steps_persistent");
+}
+
+// ------------------------------------------------------------------------------------------
+// fused data-parallel communicator: one symmetric buffer per GPU, mapped into every peer process
+// ------------------------------------------------------------------------------------------
+struct ddpm_comm {
+    int rank = 0, world = 1, device = 0;
+    void* local = nullptr;                       // cudaMalloc'd: receive buffer [2][world][NP] x 8 B | i32 error
+    size_t recv_bytes = 0;
+    void* peer[DDPM_MAX_WORLD] = {};             // peer[r]: rank r's buffer in this process's address space
+    bool opened[DDPM_MAX_WORLD] = {};
+    unsigned long long steps = 0;                // fused steps run so far (same on every rank)
+};
+
+extern "C" int ddpm_comm_create(int rank, int world, ddpm_comm** out) {
+    DDPM_CHECK_ARG(out != nullptr, "ddpm_comm_create: null output");
+    *out = nullptr;
+    DDPM_CHECK_ARG(world >= 1 && world <= DDPM_MAX_WORLD && rank >= 0 && rank < world,
+                   "ddpm_comm_create: rank %d / world %d unsupported (world <= %d: one NVLink domain)", rank, world,
+                   DDPM_MAX_WORLD);
+    ddpm_comm* c = new ddpm_comm();
+    c->rank = rank; c->world = world;
+    DDPM_CUDA(cudaGetDevice(&c->device));
+    c->recv_bytes = 2 * (size_t)world * NP * sizeof(unsigned long long);     // 15 MB at world 8
+    cudaError_t e = cudaMalloc(&c->local, c->recv_bytes + 256);
+    if (e != cudaSuccess) { delete c; return set_error("ddpm_comm_create: cudaMalloc failed: %s", cudaGetErrorString(e)); }
+    e = cudaMemset(c->local, 0, c->recv_bytes + 256);       // step field 0 never matches a real step (steps start at 1)
+    if (e != cudaSuccess) { cudaFree(c->local); delete c; return set_error("ddpm_comm_create: cudaMemset failed: %s", cudaGetErrorString(e)); }
+    c->peer[rank] = c->local;
+    *out = c;
+    return 0;
+}
+
+extern "C" int ddpm_comm_ipc_handle(const ddpm_comm* c, void* h_out64) {
+    DDPM_CHECK_ARG(c && h_out64, "ddpm_comm_ipc_handle: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DDPM_CUDA(cudaIpcGetMemHandle((cudaIpcMemHandle_t*)h_out64, c->local));
+    return 0;
+}
+
+extern "C" int ddpm_comm_connect(ddpm_comm* c, const void* h_handles) {
+    DDPM_CHECK_ARG(c && h_handles, "ddpm_comm_connect: null argument");
+    const cudaIpcMemHandle_t* hs = (const cudaIpcMemHandle_t*)h_handles;
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank || c->opened[r]) continue;
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, hs[r], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess)
+            return set_error("ddpm_comm_connect: cannot map rank %d's buffer (%s); the fused data-parallel step needs "
+                             "peer access between all GPUs of the job", r, cudaGetErrorString(e));
+        c->peer[r] = p; c->opened[r] = true;
+    }
+    return 0;
+}
+
+extern "C" int ddpm_comm_error(const ddpm_comm* c, int* h_err) {
+    DDPM_CHECK_ARG(c && h_err, "ddpm_comm_error: null argument");
+    DDPM_CUDA(cudaMemcpy(h_err, (char*)c->local + c->recv_bytes, sizeof(int), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" void ddpm_comm_destroy(ddpm_comm* c) {
+    if (!c) return;
+    for (int r = 0; r < c->world; ++r)
+        if (c->opened[r]) cudaIpcCloseMemHandle(c->peer[r]);
+    if (c->local) cudaFree(c->local);
+    delete c;
+}
+
+extern "C" int ddpm_train_steps_fused_ddp(
+        ddpm_comm* comm, float* d_params,
+        const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+        const int64_t* d_idx, const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
+        int batch, int nsteps, unsigned flags, float lr,
+        float* d_loss, float* d_loss_steps, void* d_workspace, void* stream) {
+    DDPM_CHECK_ARG(comm != nullptr, "ddpm_train_steps_fused_ddp: null communicator");
+    DDPM_CHECK_ARG(lr != 0.f, "ddpm_train_steps_fused_ddp: lr must be non-zero (the update is part of the exchange)");
+    for (int r = 0; r < comm->world; ++r)
+        DDPM_CHECK_ARG(comm->peer[r] != nullptr, "ddpm_train_steps_fused_ddp: rank %d is not connected (ddpm_comm_connect)", r);
+    PersistArgs a;
+    memset(&a, 0, sizeof(a));
+    a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
+    for (int r = 0; r < comm->world; ++r) a.xrecv[r] = (unsigned long long*)comm->peer[r];
+    a.xerr = (int*)((char*)comm->local + comm->recv_bytes);
+    const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,
+                                           philox_seed, philox_step0, batch, nsteps, flags, 1.0f / (float)comm->world, lr,
+                                           d_loss, d_loss_steps, d_workspace, stream, "ddpm_train_steps_fused_ddp");
+    if (rc == 0) comm->steps += (unsigned long long)nsteps;
+    return rc;
 }

@@ -54,6 +54,7 @@ class TrainEngine:
         self.loss = torch.zeros(2, dtype=torch.float32, device=self.device)
         self.ws = ops.Workspace(self.max_batch, self.device)
         self.step_count = 0                       # Philox stream position (perf-mode dropout)
+        self.comm = None                          # fused data-parallel communicator (enable_fused_ddp)
 
     # ------------------------------------------------------------------ parameters
     def views(self, flat: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
@@ -80,6 +81,16 @@ class TrainEngine:
         if self.world_size > 1:
             import torch.distributed as dist
             dist.broadcast(self.params, src=src, group=self.group)
+
+    def enable_fused_ddp(self) -> None:
+        """Switch the ws > 1 path from `kernel -> NCCL allreduce -> SGD kernel` per step to the fused
+        kernel (gradient exchange over NVLink peer memory inside the persistent step kernel)."""
+        if self.world_size > 1 and self.comm is None:
+            self.comm = ops.FusedComm(self.rank, self.world_size, self.group)
+
+    def check_comm(self) -> None:
+        if self.comm is not None and self.comm.error():
+            raise RuntimeError("fused data-parallel step: a peer did not show up within the exchange timeout")
 
     # ------------------------------------------------------------------ steps
     def train_step(self, resident, idx: torch.Tensor, mask: Optional[torch.Tensor] = None,
@@ -126,6 +137,11 @@ class TrainEngine:
             mk = dict(masks=masks) if masks is not None else dict(philox=(self.seed, st0))
             ops.train_steps_persistent(self.params, self.ws, batch, nsteps, idx=idx_flat, lr=self.lr,
                                        loss=self.loss, loss_steps=loss_steps, **mk, **kw)
+            return
+        if self.comm is not None:
+            mk = dict(masks=masks) if masks is not None else dict(philox=(self.seed, st0))
+            ops.train_steps_fused_ddp(self.comm, self.params, self.ws, batch, nsteps, idx=idx_flat, lr=self.lr,
+                                      loss=self.loss, loss_steps=loss_steps, **mk, **kw)
             return
         import torch.distributed as dist
         for t in range(nsteps):

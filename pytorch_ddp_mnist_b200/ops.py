@@ -12,7 +12,8 @@ from . import _lib
 from ._lib import CLASSES, HID, IN, N_PARAMS, check, cur_stream, lib, ptr
 
 __all__ = ["decode_lut", "gather_decode", "dropout_mask_philox", "Workspace", "step_forward",
-           "step_backward", "train_steps_persistent", "cross_entropy", "sgd_step"]
+           "step_backward", "train_steps_persistent", "train_steps_fused_ddp", "FusedComm", "cross_entropy",
+           "sgd_step"]
 
 
 def _need(t: Optional[torch.Tensor], name: str, dtype, shape=None, optional=False):
@@ -163,6 +164,68 @@ def train_steps_persistent(params: torch.Tensor, ws: Workspace, batch: int, nste
     check(lib.ddpm_train_steps_persistent(ptr(params), ptr(grads), ptr(images), ptr(labels), n, ptr(idx),
                                           ptr(masks), seed, step0, batch, nsteps, flags, grad_scale, lr,
                                           ptr(loss), ptr(loss_steps), ptr(ws.buf), cur_stream()))
+
+
+class FusedComm:
+    """Communicator of the fused data-parallel step (ddpm_comm_*): a symmetric device buffer per
+    rank, mapped into every peer process with CUDA IPC.  Handles travel over torch.distributed."""
+
+    def __init__(self, rank: int, world: int, group=None):
+        import ctypes as C
+        import torch.distributed as dist
+        self.rank, self.world = rank, world
+        self._h = C.c_void_p()
+        check(lib.ddpm_comm_create(rank, world, C.byref(self._h)))
+        mine = (C.c_ubyte * 64)()
+        check(lib.ddpm_comm_ipc_handle(self._h, mine))
+        gathered = [None] * world
+        dist.all_gather_object(gathered, bytes(mine), group=group)
+        blob = (C.c_ubyte * (64 * world)).from_buffer_copy(b"".join(gathered))
+        check(lib.ddpm_comm_connect(self._h, blob))
+        dist.barrier(group=group)                         # everyone is mapped before anyone launches
+
+    def error(self) -> int:
+        import ctypes as C
+        e = C.c_int(0)
+        check(lib.ddpm_comm_error(self._h, C.byref(e)))
+        return e.value
+
+    def close(self) -> None:
+        if self._h:
+            lib.ddpm_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def train_steps_fused_ddp(comm: FusedComm, params: torch.Tensor, ws: Workspace, batch: int, nsteps: int, *,
+                          images: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor,
+                          masks: Optional[torch.Tensor] = None, philox: Optional[Tuple[int, int]] = None,
+                          lr: float, loss: Optional[torch.Tensor] = None,
+                          loss_steps: Optional[torch.Tensor] = None) -> None:
+    """`nsteps` data-parallel optimisation steps in one launch per rank; the gradient average and
+    the update happen inside the kernel over NVLink peer memory."""
+    _need(params, "params", torch.float32, (N_PARAMS,))
+    if batch > ws.max_batch:
+        raise ValueError(f"batch {batch} exceeds workspace max_batch {ws.max_batch}")
+    _need(images, "images", torch.uint8)
+    n = images.shape[0]
+    _need(labels, "labels", torch.uint8, (n,))
+    _need(idx, "idx", torch.int64)
+    if idx.numel() < nsteps * batch:
+        raise ValueError("idx shorter than nsteps*batch")
+    _need(masks, "masks", torch.uint8, (nsteps, batch, HID), optional=True)
+    _need(loss, "loss", torch.float32, (2,), optional=True)
+    _need(loss_steps, "loss_steps", torch.float32, optional=True)
+    seed, step0 = philox if philox else (0, 0)
+    flags = _lib.FWD_PHILOX_MASK if philox else 0
+    check(lib.ddpm_train_steps_fused_ddp(comm._h, ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(masks),
+                                         seed, step0, batch, nsteps, flags, lr, ptr(loss), ptr(loss_steps),
+                                         ptr(ws.buf), cur_stream()))
 
 
 def cross_entropy(logits: torch.Tensor, y: torch.Tensor, loss: Optional[torch.Tensor] = None,
