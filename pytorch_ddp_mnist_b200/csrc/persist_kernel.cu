@@ -22,6 +22,7 @@
 // Every sum has a fixed order: results are bit-identical run to run and independent of timing.
 #include <cooperative_groups.h>
 #include <cuda_pipeline.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -56,7 +57,7 @@ struct PersistArgs {
     unsigned long long* bar;                          // [0] monotonic arrival counter, [1] monotonic 'W2/W3/b ready' counter
     long long* dbg;                                   // optional [grid][8 steps][16] clock64 stamps (profiling aid)
     // ---- fused data-parallel mode (world > 1): gradient tiles are exchanged over NVLink peer memory
-    int world, rank;
+    int world, rank, two_stage;
     unsigned long long comm_step;                     // number of fused steps this communicator ran before this launch
     unsigned long long* xrecv[DDPM_MAX_WORLD];        // every rank's receive buffer [2 parities][world sources][NP] of
                                                       // 8-byte (value, step) words, peer-mapped
@@ -189,59 +190,73 @@ __device__ __forceinline__ void grad_out(float* gout, float lr, float* params, i
 // (local) receive buffer, summing in rank order — identical on all ranks, hence bit-identical
 // replicas.  Slots are double-buffered by step parity: a rank can only be one step ahead of a peer.
 template <int N>
-__device__ __forceinline__ void ll_send(const PersistArgs& a, unsigned long long T, int off, const float (&v)[N]) {
-    const unsigned t32 = (unsigned)T;
-    const size_t slot = ((size_t)(T & 1) * a.world + a.rank) * NP + off;
-    for (int r = 0; r < a.world; ++r) {
-        if (r == a.rank) continue;
-        unsigned long long* dst = a.xrecv[r] + slot;
-        if (N == 1) {
-            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"(__float_as_uint(v[0])), "r"(t32) : "memory");
-        } else {
+__device__ __forceinline__ void ll_store(unsigned long long* dst, unsigned t32, const float (&v)[N]) {
+    if (N == 1) {
+        asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"(__float_as_uint(v[0])), "r"(t32) : "memory");
+    } else {
 #pragma unroll
-            for (int i = 0; i < N; i += 2)
-                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst + i), "r"(__float_as_uint(v[i])),
-                             "r"(t32), "r"(__float_as_uint(v[i + (N > 1 ? 1 : 0)])), "r"(t32) : "memory");
+        for (int i = 0; i < N; i += 2)
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst + i), "r"(__float_as_uint(v[i])),
+                         "r"(t32), "r"(__float_as_uint(v[i + (N > 1 ? 1 : 0)])), "r"(t32) : "memory");
+    }
+}
+template <int N>
+__device__ __forceinline__ void ll_poll(const PersistArgs& a, const unsigned long long* src, unsigned t32, long long t0,
+                                        float (&got)[N]) {
+    if (N == 1) {
+        unsigned x, f;
+        do {
+            asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
+            if (f != t32 && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }              // ~3 s: peer missing
+        } while (f != t32);
+        got[0] = __uint_as_float(x);
+    } else {
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            unsigned x0, f0, x1, f1;
+            do {
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(f0), "=r"(x1), "=r"(f1)
+                             : "l"(src + i) : "memory");
+                if ((f0 != t32 || f1 != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
+            } while (f0 != t32 || f1 != t32);
+            got[i] = __uint_as_float(x0); got[i + (N > 1 ? 1 : 0)] = __uint_as_float(x1);
         }
     }
 }
-// v holds this rank's own contribution on entry and the sum over all ranks (rank order) on exit.
+// v: this rank's contribution on entry, the sum over all ranks (rank order) on exit.
+//   one-shot  (a.two_stage == 0): everyone pushes to everyone, everyone sums: 1 NVLink hop, (ws-1) x bytes
+//   two-stage (a.two_stage == 1): the elements of CTA `cta` have a home rank cta % ws; the others push their
+//             contribution to the home, the home sums and pushes the result back: 2 hops, 2(ws-1)/ws x bytes
 template <int N>
-__device__ __forceinline__ void ll_reduce(const PersistArgs& a, unsigned long long T, int off, float (&v)[N]) {
+__device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int cta, int off, float (&v)[N]) {
     const unsigned t32 = (unsigned)T;
-    float own[N], sum[N];
-#pragma unroll
-    for (int i = 0; i < N; ++i) { own[i] = v[i]; sum[i] = 0.f; }
+    const size_t par = (size_t)(T & 1) * a.world;
     const long long t0 = clock64();
+    const int home = cta % a.world;
+    if (a.two_stage && a.rank != home) {
+        ll_store<N>(a.xrecv[home] + (par + a.rank) * NP + off, t32, v);
+        ll_poll<N>(a, a.xrecv[a.rank] + (par + home) * NP + off, t32, t0, v);
+        return;
+    }
+    if (!a.two_stage) {
+        for (int r = 0; r < a.world; ++r)
+            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
+    }
+    float sum[N];
     for (int r = 0; r < a.world; ++r) {
         float got[N];
         if (r == a.rank) {
 #pragma unroll
-            for (int i = 0; i < N; ++i) got[i] = own[i];
+            for (int i = 0; i < N; ++i) got[i] = v[i];
         } else {
-            const unsigned long long* src = a.xrecv[a.rank] + ((size_t)(T & 1) * a.world + r) * NP + off;
-            if (N == 1) {
-                unsigned x, f;
-                do {
-                    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
-                    if (f != t32 && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }      // ~3 s: peer missing
-                } while (f != t32);
-                got[0] = __uint_as_float(x);
-            } else {
-#pragma unroll
-                for (int i = 0; i < N; i += 2) {
-                    unsigned x0, f0, x1, f1;
-                    do {
-                        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(f0), "=r"(x1), "=r"(f1)
-                                     : "l"(src + i) : "memory");
-                        if ((f0 != t32 || f1 != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
-                    } while (f0 != t32 || f1 != t32);
-                    got[i] = __uint_as_float(x0); got[i + (N > 1 ? 1 : 0)] = __uint_as_float(x1);
-                }
-            }
+            ll_poll<N>(a, a.xrecv[a.rank] + (par + r) * NP + off, t32, t0, got);
         }
 #pragma unroll
         for (int i = 0; i < N; ++i) sum[i] = (r == 0) ? got[i] : sum[i] + got[i];
+    }
+    if (a.two_stage) {
+        for (int r = 0; r < a.world; ++r)
+            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
     }
 #pragma unroll
     for (int i = 0; i < N; ++i) v[i] = sum[i];
@@ -572,7 +587,7 @@ train_persist_kernel(PersistArgs a) {
                 const int offb = DDPM_OFF_B1 + mt * MT + (tid - 224);
                 float gb[1] = {db_acc * a.gscale};
                 const float pold = __ldcg(a.params + offb);
-                if (ddp) { ll_send<1>(a, T, offb, gb); ll_reduce<1>(a, T, offb, gb); }
+                if (ddp) ll_allreduce<1>(a, T, cta, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pold);
             }
             float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
@@ -596,9 +611,8 @@ train_persist_kernel(PersistArgs a) {
                 g[3] = ((p[0].w + p[1].w) + (p[2].w + p[3].w)) * a.gscale;
                 const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
                 if (ddp) {                                      // push to every peer, then sum everyone's tile
-                    ll_send<4>(a, T, off, g);
                     DBG_STAMP(11);
-                    ll_reduce<4>(a, T, off, g);
+                    ll_allreduce<4>(a, T, cta, off, g);
                     DBG_STAMP(12);
                 }
                 if (a.grads) *reinterpret_cast<float4*>(a.grads + off) = make_float4(g[0], g[1], g[2], g[3]);
@@ -668,14 +682,14 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
                 float g[2] = {((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale,
                               ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale};
-                if (ddp) { ll_send<2>(a, T, off, g); ll_reduce<2>(a, T, off, g); }
+                if (ddp) ll_allreduce<2>(a, T, cta, off, g);
                 grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
                 grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
             }
             if (do_db) {
                 const int offb = DDPM_OFF_B2 + jt * 16 + tid;
                 float gb[1] = {db_acc * a.gscale};
-                if (ddp) { ll_send<1>(a, T, offb, gb); ll_reduce<1>(a, T, offb, gb); }
+                if (ddp) ll_allreduce<1>(a, T, cta, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
             }
         } else {
@@ -733,13 +747,13 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
                 const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
                 float ga[1] = {g0 * a.gscale};
-                if (ddp) { ll_send<1>(a, T, o0, ga); ll_reduce<1>(a, T, o0, ga); }
+                if (ddp) ll_allreduce<1>(a, T, cta, o0, ga);
                 grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) {
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
                     float gc[1] = {g1 * a.gscale};
-                    if (ddp) { ll_send<1>(a, T, o1, gc); ll_reduce<1>(a, T, o1, gc); }
+                    if (ddp) ll_allreduce<1>(a, T, cta, o1, gc);
                     grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
                 }
             }
@@ -869,6 +883,7 @@ struct ddpm_comm {
     void* peer[DDPM_MAX_WORLD] = {};             // peer[r]: rank r's buffer in this process's address space
     bool opened[DDPM_MAX_WORLD] = {};
     unsigned long long steps = 0;                // fused steps run so far (same on every rank)
+    int two_stage = 0;                           // exchange algorithm (see ll_allreduce)
 };
 
 extern "C" int ddpm_comm_create(int rank, int world, ddpm_comm** out) {
@@ -879,6 +894,10 @@ extern "C" int ddpm_comm_create(int rank, int world, ddpm_comm** out) {
                    DDPM_MAX_WORLD);
     ddpm_comm* c = new ddpm_comm();
     c->rank = rank; c->world = world;
+    {   // default: one hop while the (ws-1)x traffic is small, two hops with 2(ws-1)/ws x traffic beyond that
+        const char* e = getenv("DDPM_EXCHANGE");
+        c->two_stage = e ? (strcmp(e, "two_stage") == 0) : (world > 2);
+    }
     DDPM_CUDA(cudaGetDevice(&c->device));
     c->recv_bytes = 2 * (size_t)world * NP * sizeof(unsigned long long);     // 15 MB at world 8
     cudaError_t e = cudaMalloc(&c->local, c->recv_bytes + 256);
@@ -939,6 +958,7 @@ extern "C" int ddpm_train_steps_fused_ddp(
     PersistArgs a;
     memset(&a, 0, sizeof(a));
     a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
+    a.two_stage = comm->two_stage;
     for (int r = 0; r < comm->world; ++r) a.xrecv[r] = (unsigned long long*)comm->peer[r];
     a.xerr = (int*)((char*)comm->local + comm->recv_bytes);
     const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,

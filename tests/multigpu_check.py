@@ -31,24 +31,32 @@ def main():
     if rank == 0:
         eng.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
     eng.broadcast_params(0)                                # DDP wrap: everyone adopts rank 0's
-    masks = torch.from_numpy(O.unpack_masks(g[f"rank{rank}.masks"])).to(dev)
-    idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
-    assert np.array_equal(g[f"rank{rank}.idx"][0], O.shard_indices(60000, world, rank)[:64])
+    golden_ws = (world == 2)
+    if golden_ws:
+        masks = torch.from_numpy(O.unpack_masks(g[f"rank{rank}.masks"])).to(dev)
+        idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
+        assert np.array_equal(g[f"rank{rank}.idx"][0], O.shard_indices(60000, world, rank)[:64])
+        ref = g[f"rank{rank}.losses"]
+    else:                                   # no reference run at this world size: self-consistency only
+        rng = np.random.default_rng(500 + rank)
+        masks = torch.from_numpy((rng.random((20, 64, 128)) < 0.8).astype(np.uint8)).to(dev)
+        idx = torch.from_numpy(O.shard_indices(60000, world, rank)[:20 * 64].reshape(20, 64)).to(dev)
+        ref = None
     losses = []
     for t in range(idx.shape[0]):
         eng.train_step(res, idx[t], mask=masks[t])
         losses.append(eng.last_batch_loss())
-        if t == 0:
-            pass
-    ref = g[f"rank{rank}.losses"]
-    err = np.abs(np.array(losses) - ref).max()
-    assert err < 5e-3 * np.abs(ref).max(), (rank, err)
-    assert np.abs(np.array(losses[:3]) - ref[:3]).max() < 1e-5
-    pu = O.unflatten_params(eng.params.cpu().numpy())
-    for k in O.PARAM_KEYS:
-        r = g[f"paramsN.{k}"].astype(np.float64)
-        fro = np.linalg.norm(pu[k] - r) / np.linalg.norm(r)
-        assert fro < 5e-3, (k, fro)
+    err = 0.0
+    if golden_ws:
+        err = np.abs(np.array(losses) - ref).max()
+        assert err < 5e-3 * np.abs(ref).max(), (rank, err)
+        assert np.abs(np.array(losses[:3]) - ref[:3]).max() < 1e-5
+        pu = O.unflatten_params(eng.params.cpu().numpy())
+        for k in O.PARAM_KEYS:
+            r = g[f"paramsN.{k}"].astype(np.float64)
+            fro = np.linalg.norm(pu[k] - r) / np.linalg.norm(r)
+            assert fro < 5e-3, (k, fro)
+    ref = np.array(losses, np.float32)      # the NCCL path is the yardstick for the fused path below
     # replicas stay bit-identical
     mine = eng.params.clone()
     other = mine.clone()
@@ -65,7 +73,7 @@ def main():
     torch.cuda.synchronize()
     eng2.check_comm()
     l2 = ls.cpu().numpy()
-    assert np.abs(l2 - ref).max() < 5e-3 * np.abs(ref).max(), (rank, np.abs(l2 - ref).max())
+    assert np.abs(l2 - ref).max() < 1e-4 * np.abs(ref).max(), (rank, np.abs(l2 - ref).max())
     assert np.abs(l2[:3] - ref[:3]).max() < 1e-5
     rel = float((eng2.params - eng.params).abs().max() / eng.params.abs().max())
     assert rel < 1e-4, ("fused vs NCCL path", rel)            # same math, different summation order
@@ -83,7 +91,8 @@ def main():
     assert torch.equal(mine, other), "fused replicas diverged after the second launch"
     dist.barrier()
     if rank == 0:
-        print("MULTIGPU_OK max loss err %.2e fused-vs-nccl %.2e" % (err, rel))
+        print("MULTIGPU_OK world %d exchange %s max loss err %.2e fused-vs-nccl %.2e" %
+              (world, os.environ.get("DDPM_EXCHANGE", "default"), err, rel))
     dist.destroy_process_group()
 
 
