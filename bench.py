@@ -30,6 +30,24 @@ BENCH_SEED = 1234
 CHUNK = 100                # steps unrolled per CUDA graph
 
 
+def _ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one 1-step launch of train_persist_kernel, from the
+    committed `ncu --set full` capture (profiles/r01_v2_ncu_full_summary.csv); None if absent."""
+    import csv
+    p = os.path.join(REPO, "profiles", "r01_v2_ncu_full_summary.csv")
+    try:
+        rows = list(csv.reader(open(p)))
+        hdr, units, r = rows[0], rows[1], rows[2]
+        mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = 0.0
+        for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = hdr.index(name)
+            tot += float(r[i]) * mult[units[i]]
+        return tot
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(REPO, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -354,7 +372,7 @@ def _time_kernels(torch, ops, eng, resident, shard_dev, B, world, three_kernel=F
     ]
     dom = kernels[0] if (t_persist and not three_kernel) else max(kernels[1:3], key=lambda k: k["ms"])
     roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": hbm, "unit": "GB/s", "frac": dom["gbs"] / hbm,
-            "traffic": None, "kernel": dom["name"], "peak_source": which,
+            "traffic": _ncu_traffic() if dom is kernels[0] else None, "kernel": dom["name"], "peak_source": which,
             "note": "algorithmic bytes = what one step must move (DESIGN.md §4); batch-64 steps are latency-bound "
                     "(2 grid barriers + dependent round trips per step), not bandwidth-bound"}
     return {"kernels": kernels, "roofline": roof}
