@@ -200,15 +200,19 @@ class DeviceBatchLoader:
     def __len__(self) -> int:
         return len(self._index_loader)
 
-    def index_batches(self) -> Iterator[torch.Tensor]:
-        """The epoch's batches as int64 index tensors on the device (one upload per epoch)."""
-        it = iter(self._index_loader)               # consumes the global RNG like the reference
-        batches = [b for b in it]
+    def epoch_indices(self) -> Tuple[torch.Tensor, list]:
+        """(flat i64 index tensor on the device, list of batch sizes) for one epoch: one upload.
+        Iterating the index loader consumes the global RNG exactly like the reference's loader."""
+        batches = [b for b in iter(self._index_loader)]
         if not batches:
-            return iter(())
+            return torch.empty(0, dtype=torch.int64, device=self.resident.device), []
         flat = torch.cat(batches).to(self.resident.device, non_blocking=True)
-        sizes = [len(b) for b in batches]
-        return iter(torch.split(flat, sizes))
+        return flat, [len(b) for b in batches]
+
+    def index_batches(self) -> Iterator[torch.Tensor]:
+        """The epoch's batches as int64 index tensors on the device."""
+        flat, sizes = self.epoch_indices()
+        return iter(torch.split(flat, sizes)) if sizes else iter(())
 
     def __iter__(self):
         r = self.resident

@@ -121,20 +121,34 @@ def main(model: nn.Module, train_loader: DeviceBatchLoader, test_loader: DeviceB
     eng = TrainEngine(device, batch, lr=0.01, world_size=world_size, rank=rank)
     eng.load_state_dict(model.state_dict())
     eng.broadcast_params(0)                              # DistributedDataParallel(model), mp:439
+    if world_size > 1 and batch <= 512:
+        eng.enable_fused_ddp()                           # gradient average inside the step kernel (NVLink peer memory)
     train_res, test_res = train_loader.resident, test_loader.resident
     step_no = 0
     for i in range(epochs):
         model.train()
         train_loader.sampler.set_epoch(i)                # mp:449
         eng.zero_epoch_loss()
-        for n, idx in enumerate(train_loader.index_batches()):
-            mask = None
+        flat, sizes = train_loader.epoch_indices()
+        # consecutive equal-sized batches go to the device as ONE launch of the persistent kernel
+        # (`progress` splits the epoch into chunks so a loss can be shown); the short last batch is its own launch
+        pos, n = 0, 0
+        while n < len(sizes):
+            b = sizes[n]
+            m = n
+            while m < len(sizes) and sizes[m] == b and (not progress or m - n < progress):
+                m += 1
+            k = m - n
+            masks = None
             if mask_fn is not None:
-                mask = mask_fn(step_no, idx.numel()).to(device, torch.uint8).contiguous()
-            eng.train_step(train_res, idx, mask=mask)
-            step_no += 1
-            if progress and rank == 0 and (n + 1) % progress == 0:
-                print(f'training batch_loss={eng.last_batch_loss():.4f} [{n + 1}/{len(train_loader)}]')
+                masks = torch.stack([mask_fn(step_no + t, b) for t in range(k)]).to(device, torch.uint8).contiguous()
+            eng.train_steps(train_res, flat[pos:pos + k * b], b, k, masks=masks)
+            step_no += k
+            pos += k * b
+            n = m
+            if progress and rank == 0:
+                print(f'training batch_loss={eng.last_batch_loss():.4f} [{n}/{len(sizes)}]')
+        eng.check_comm()
         epoch_loss = eng.epoch_loss()
         with torch.no_grad():
             model.eval()
