@@ -81,6 +81,9 @@ int    ddpm_workspace_init(void* d_workspace, int max_batch, void* stream);
 
 #define DDPM_FWD_PREP_BACKWARD 1u  /* also compute dL/dz2, dL/dz1 from the CE gradient (training) */
 #define DDPM_FWD_PHILOX_MASK   2u  /* draw the dropout mask in-kernel (seed, step); d_mask unused */
+#define DDPM_FWD_TF32          4u  /* fc1 on the tcgen05 tensor cores: TF32 operands, FP32 accumulate in TMEM
+                                      (csrc/fc1_tc.cu).  Results agree with the fp32 path to ~1e-3 relative
+                                      instead of 2e-5; worthwhile for large batches only.  Needs d_x == NULL. */
 
 /* Forward of create_model() + CrossEntropyLoss (mp:412-422, mp:460-461; eval form mp:476-477).
  * Input rows come either from the resident u8 dataset through d_idx (d_x == NULL; the decode is

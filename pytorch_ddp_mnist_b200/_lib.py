@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libddpmnist_b200.so")
 
 IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
-FWD_PREP_BACKWARD, FWD_PHILOX_MASK = 1, 2
+FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
 ABI_VERSION = 1

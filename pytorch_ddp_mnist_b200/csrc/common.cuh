@@ -86,10 +86,17 @@ struct WsLayout {
     size_t dz3;       // f32 [B][16]   dL/dlogits, zero padded
     size_t rowloss;   // f32 [B]
     size_t yb;        // u8  [B]
+    size_t gpart;     // f32 [bsplit][NP] partial gradients of the batch slices (batch >= 1024 only)
     size_t total;
 };
 int fc1_ksplit(int batch);              // how many K splits G1 uses for this batch
+int grads_bsplit(int batch);            // how many batch slices grads_kernel uses
 size_t part1_rows_capacity(int max_batch);
 WsLayout ws_layout(int max_batch);
+
+// fc1 forward on tcgen05 tensor cores (csrc/fc1_tc.cu)
+int fc1_tc_ksplit();
+int launch_fc1_tc(const float* W1, const uint8_t* images, int64_t n_samples, const int64_t* idx, int B, float* part,
+                  cudaStream_t st);
 
 }  // namespace ddpm

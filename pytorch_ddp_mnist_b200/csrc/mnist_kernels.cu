@@ -34,6 +34,9 @@ constexpr int G1_BM_LARGE = 64, G1_BN_LARGE = 128;
 constexpr int G1_LARGE_BATCH = 1024;
 constexpr int TARGET_ITEMS = 296;                 // 2 x 148 SMs
 
+// grads_kernel cuts large batches into slices so that more than 67 CTAs have work
+int grads_bsplit(int batch) { return batch >= 1024 ? (batch / 256 < 16 ? batch / 256 : 16) : 1; }
+
 int fc1_ksplit(int batch) {
     const bool large = batch >= G1_LARGE_BATCH;
     const int bm = large ? G1_BM_LARGE : G1_BM_SMALL, bn = large ? G1_BN_LARGE : G1_BN_SMALL;
@@ -83,6 +86,7 @@ static WsLayout ws_layout_compute(int max_batch) {
     L.dz3 = off;     off = al256(off + B * NCP * sizeof(float));
     L.rowloss = off; off = al256(off + B * sizeof(float));
     L.yb = off;      off = al256(off + B);
+    L.gpart = off;   off = al256(off + (grads_bsplit(max_batch) > 1 ? (size_t)grads_bsplit(max_batch) * NP * sizeof(float) : 0));
     L.total = off;
     return L;
 }
@@ -498,6 +502,7 @@ struct GradArgs {
     const uint8_t* images; int64_t n_samples; const int64_t* idx; const float* x;
     const float* h1d; const float* h2; const float* dz1; const float* dz2; const float* dz3;
     int B; float scale, lr;
+    int bsplit; float* gpart;          // large batches: the batch is cut in bsplit slices, raw partial gradients [bsplit][NP]
 };
 
 __device__ __forceinline__ void grad_store4(const GradArgs& a, int off, float4 g) {
@@ -518,7 +523,7 @@ __device__ __forceinline__ void grad_store1(const GradArgs& a, int off, float g)
 template <int BM, int BN, int TM, int TN, bool U8>
 __device__ void grad_tile(const GradArgs& a, const float* __restrict__ A, int lda, int m0, int M,
                           const float* __restrict__ Bf, int ldb, int n0, int c_off, int ldc,
-                          float* As, float* Bs, const float* lut) {
+                          float* As, float* Bs, const float* lut, int b_begin, int b_end, int bs) {
     constexpr int TX = BN / TN, TY = BM / TM;
     static_assert(TX * TY <= 256, "tile too large for 256 threads");
     static_assert(TN == 4 || TN == 8, "TN");
@@ -526,14 +531,14 @@ __device__ void grad_tile(const GradArgs& a, const float* __restrict__ A, int ld
     const int tid = threadIdx.x;
     const bool active = tid < TX * TY;
     const int tx = tid % TX, ty = tid / TX;
-    const int B = a.B;
+    const int B = b_end;                 // rows at or past the end of this batch slice read as zero
     float acc[TM][TN];
 #pragma unroll
     for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
-    for (int k0 = 0; k0 < B; k0 += KCHUNK) {
+    for (int k0 = b_begin; k0 < B; k0 += KCHUNK) {
         __syncthreads();
         for (int t = tid; t < KCHUNK * (BM / 4); t += 256) {
             const int k = t / (BM / 4), q = t - k * (BM / 4), b = k0 + k;
@@ -593,9 +598,15 @@ __device__ void grad_tile(const GradArgs& a, const float* __restrict__ A, int ld
             if (m < M) {
 #pragma unroll
                 for (int j4 = 0; j4 < TN / 4; ++j4) {
-                    float4 g = make_float4(acc[i][j4 * 4] * a.scale, acc[i][j4 * 4 + 1] * a.scale,
-                                           acc[i][j4 * 4 + 2] * a.scale, acc[i][j4 * 4 + 3] * a.scale);
-                    grad_store4(a, c_off + m * ldc + n0 + tx * TN + j4 * 4, g);
+                    const int off = c_off + m * ldc + n0 + tx * TN + j4 * 4;
+                    if (a.bsplit > 1) {       // raw partial sum of this batch slice; grads_finalize_kernel combines them
+                        *reinterpret_cast<float4*>(a.gpart + (size_t)bs * NP + off) =
+                            make_float4(acc[i][j4 * 4], acc[i][j4 * 4 + 1], acc[i][j4 * 4 + 2], acc[i][j4 * 4 + 3]);
+                    } else {
+                        float4 g = make_float4(acc[i][j4 * 4] * a.scale, acc[i][j4 * 4 + 1] * a.scale,
+                                               acc[i][j4 * 4 + 2] * a.scale, acc[i][j4 * 4 + 3] * a.scale);
+                        grad_store4(a, off, g);
+                    }
                 }
             }
         }
@@ -615,31 +626,52 @@ grads_kernel(GradArgs a) {
     __shared__ __align__(16) float Bs[KCHUNK * (HID + 4)];
     __shared__ float lut[256];
     if (U8) lut[threadIdx.x] = decode_px(threadIdx.x);
-    for (int item = blockIdx.x; item < GRAD_ITEMS; item += gridDim.x) {
+    const int slice = (a.B + a.bsplit - 1) / a.bsplit;
+    for (int work = blockIdx.x; work < GRAD_ITEMS * a.bsplit; work += gridDim.x) {
+        const int bs = work / GRAD_ITEMS, item = work - bs * GRAD_ITEMS;
+        const int b0 = bs * slice, b1 = min(a.B, b0 + slice);
         if (item < N_GW1) {
             const int mt = item / (IN / GW1_BN), nt = item - mt * (IN / GW1_BN);
             grad_tile<GW1_BM, GW1_BN, 2, 4, U8>(a, a.dz1, HID, mt * GW1_BM, HID, a.x, IN, nt * GW1_BN,
-                                                DDPM_OFF_W1, IN, As, Bs, lut);
+                                                DDPM_OFF_W1, IN, As, Bs, lut, b0, b1, bs);
         } else if (item < N_GW1 + N_GW2) {
             const int t = item - N_GW1;
             const int mt = t / (HID / GW2_BN), nt = t - mt * (HID / GW2_BN);
             grad_tile<GW2_BM, GW2_BN, 2, 4, false>(a, a.dz2, HID, mt * GW2_BM, HID, a.h1d, HID, nt * GW2_BN,
-                                                   DDPM_OFF_W2, HID, As, Bs, lut);
+                                                   DDPM_OFF_W2, HID, As, Bs, lut, b0, b1, bs);
         } else if (item == N_GW1 + N_GW2) {
-            grad_tile<16, HID, 1, 8, false>(a, a.dz3, NCP, 0, NC, a.h2, HID, 0, DDPM_OFF_W3, HID, As, Bs, lut);
+            grad_tile<16, HID, 1, 8, false>(a, a.dz3, NCP, 0, NC, a.h2, HID, 0, DDPM_OFF_W3, HID, As, Bs, lut, b0, b1, bs);
         } else {
-            // bias gradients: column sums over the batch, two half-batches per column
+            // bias gradients: column sums over the batch slice, two interleaved halves per column
             const bool first = (item == N_GW1 + N_GW2 + 1);
             const float* D = first ? a.dz1 : a.dz2;
             const int off = first ? DDPM_OFF_B1 : DDPM_OFF_B2;
             const int col = threadIdx.x & 127, half = threadIdx.x >> 7;
             float v = 0.f;
-            for (int b = half; b < a.B; b += 2) v += __ldcg(D + (size_t)b * HID + col);
+            for (int b = b0 + half; b < b1; b += 2) v += __ldcg(D + (size_t)b * HID + col);
             __syncthreads();
             if (half) As[col] = v;
             __syncthreads();
-            if (!half) grad_store1(a, off + col, (v + As[col]) * a.scale);
+            if (!half) {
+                if (a.bsplit > 1) a.gpart[(size_t)bs * NP + off + col] = v + As[col];
+                else grad_store1(a, off + col, (v + As[col]) * a.scale);
+            }
         }
+    }
+}
+
+// Combine the batch slices' partial gradients in fixed order, scale, write the bucket and/or apply SGD.
+__global__ void __launch_bounds__(256)
+grads_finalize_kernel(GradArgs a) {
+    const int n4 = NP / 4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+        float4 g = __ldcg(reinterpret_cast<const float4*>(a.gpart) + i);
+        for (int s = 1; s < a.bsplit; ++s) {
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)s * NP) + i);
+            g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+        g.x *= a.scale; g.y *= a.scale; g.z *= a.scale; g.w *= a.scale;
+        grad_store4(a, i * 4, g);
     }
 }
 
@@ -813,7 +845,9 @@ int ddpm_step_forward(const float* d_params,
     DDPM_CHECK_ARG(d_params && d_workspace, "ddpm_step_forward: null params/workspace");
     DDPM_CHECK_ARG(d_x != nullptr || (d_images != nullptr && d_idx != nullptr && n_samples > 0),
                    "ddpm_step_forward: need either d_x or (d_images, d_idx, n_samples)");
-    DDPM_CHECK_ARG((flags & ~(DDPM_FWD_PREP_BACKWARD | DDPM_FWD_PHILOX_MASK)) == 0, "ddpm_step_forward: unknown flags %#x", flags);
+    DDPM_CHECK_ARG((flags & ~(DDPM_FWD_PREP_BACKWARD | DDPM_FWD_PHILOX_MASK | DDPM_FWD_TF32)) == 0, "ddpm_step_forward: unknown flags %#x", flags);
+    DDPM_CHECK_ARG(!(flags & DDPM_FWD_TF32) || d_x == nullptr,
+                   "ddpm_step_forward: DDPM_FWD_TF32 needs the resident uint8 dataset path (d_x must be NULL)");
     DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0 && ((uintptr_t)d_params & 15) == 0,
                    "ddpm_step_forward: workspace must be 256-byte and params 16-byte aligned");
     DDPM_CHECK_ARG(d_x == nullptr || ((uintptr_t)d_x & 15) == 0, "ddpm_step_forward: d_x must be 16-byte aligned");
@@ -821,9 +855,12 @@ int ddpm_step_forward(const float* d_params,
     cudaStream_t st = (cudaStream_t)stream;
     char* ws = (char*)d_workspace;
     const WsLayout L = ws_layout(batch);       // offsets depend only on the batch of THIS call
-    const int ks = fc1_ksplit(batch);
+    const bool tf32 = (flags & DDPM_FWD_TF32) != 0;
+    const int ks = tf32 ? fc1_tc_ksplit() : fc1_ksplit(batch);
     float* part = (float*)(ws + L.part1);
-    if (launch_fc1(d_params, d_images, n_samples, d_idx, d_x, batch, ks, part, nullptr, st)) return 1;
+    if (tf32) {
+        if (launch_fc1_tc(d_params + DDPM_OFF_W1, d_images, n_samples, d_idx, batch, part, st)) return 1;
+    } else if (launch_fc1(d_params, d_images, n_samples, d_idx, d_x, batch, ks, part, nullptr, st)) return 1;
     RowsArgs a;
     memset(&a, 0, sizeof(a));
     a.params = d_params; a.part = part; a.ksplit = ks;
@@ -833,7 +870,7 @@ int ddpm_step_forward(const float* d_params,
     a.labels = (d_x == nullptr) ? d_labels : nullptr;
     a.idx = (d_x == nullptr) ? d_idx : nullptr;
     a.n_samples = n_samples;
-    a.B = batch; a.flags = flags;
+    a.B = batch; a.flags = flags & ~DDPM_FWD_TF32;
     a.logits = d_logits; a.loss = d_loss;
     a.h1d = (float*)(ws + L.h1d); a.h2 = (float*)(ws + L.h2);
     a.dz2 = (float*)(ws + L.dz2); a.dz1 = (float*)(ws + L.dz1);
@@ -875,9 +912,14 @@ int ddpm_step_backward(float* d_params,
     g.dz1 = (const float*)(ws + L.dz1); g.dz2 = (const float*)(ws + L.dz2);
     g.dz3 = (const float*)(ws + L.dz3);
     g.B = batch; g.scale = grad_scale; g.lr = lr;
-    if (d_x == nullptr) grads_kernel<true><<<GRAD_ITEMS, 256, 0, st>>>(g);
-    else                grads_kernel<false><<<GRAD_ITEMS, 256, 0, st>>>(g);
+    g.bsplit = grads_bsplit(batch); g.gpart = (float*)(ws + L.gpart);
+    if (d_x == nullptr) grads_kernel<true><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
+    else                grads_kernel<false><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
     DDPM_CUDA(cudaGetLastError());
+    if (g.bsplit > 1) {
+        grads_finalize_kernel<<<116, 256, 0, st>>>(g);
+        DDPM_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 

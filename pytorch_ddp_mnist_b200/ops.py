@@ -94,7 +94,8 @@ def step_forward(params: torch.Tensor, ws: Workspace, batch: int, *,
                  idx: Optional[torch.Tensor] = None, x: Optional[torch.Tensor] = None,
                  y: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None,
                  philox: Optional[Tuple[int, int]] = None, prep_backward: bool = False,
-                 logits: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None) -> None:
+                 logits: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None,
+                 tf32: bool = False) -> None:
     _need(params, "params", torch.float32, (N_PARAMS,))
     if batch > ws.max_batch:
         raise ValueError(f"batch {batch} exceeds workspace max_batch {ws.max_batch}")
@@ -112,7 +113,8 @@ def step_forward(params: torch.Tensor, ws: Workspace, batch: int, *,
     _need(mask, "mask", torch.uint8, (batch, HID), optional=True)
     _need(logits, "logits", torch.float32, (batch, CLASSES), optional=True)
     _need(loss, "loss", torch.float32, (2,), optional=True)
-    flags = (_lib.FWD_PREP_BACKWARD if prep_backward else 0) | (_lib.FWD_PHILOX_MASK if philox else 0)
+    flags = ((_lib.FWD_PREP_BACKWARD if prep_backward else 0) | (_lib.FWD_PHILOX_MASK if philox else 0)
+             | (_lib.FWD_TF32 if tf32 else 0))
     seed, step = philox if philox else (0, 0)
     check(lib.ddpm_step_forward(ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(x), ptr(y),
                                 ptr(mask), seed, step, batch, flags, ptr(logits), ptr(loss),
