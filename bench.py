@@ -193,6 +193,15 @@ def main() -> None:
     need = (W + K + CHUNK) * B
     reps = -(-need // shard.numel())
     shard_dev = shard.repeat(reps)[:need].to(dev)          # wraps after 3750/ws steps; rows long evicted by then
+    shards_all_dev = None
+    if world > 1:                                          # every rank's shard (a pure function of seed, epoch, rank)
+        rows = []
+        for r in range(world):
+            sr = DistributedSampler(_IndexOnly(BENCH_N), num_replicas=world, rank=r, shuffle=True, seed=42)
+            sr.set_epoch(0)
+            rows.append(torch.tensor(list(iter(sr)), dtype=torch.int64).repeat(reps)[:need])
+        shards_all_dev = torch.stack(rows).to(dev)
+        assert torch.equal(shards_all_dev[rank], shard_dev)
 
     torch.manual_seed(0)
     eng = E.TrainEngine(dev, B, lr=0.01, world_size=world, rank=rank)
@@ -231,7 +240,8 @@ def main() -> None:
                 idx_buf.copy_(shard_dev[s:s + chunk * B])
                 graph.replay()
             else:
-                eng.train_steps(resident, shard_dev[s:s + chunk * B], B, chunk)
+                ia = shards_all_dev[:, s:s + chunk * B].contiguous() if (fused and shards_all_dev is not None) else None
+                eng.train_steps(resident, shard_dev[s:s + chunk * B], B, chunk, idx_all=ia)
             done += chunk
             launches += kernels_per_chunk
         while done < n_steps:                               # remainder, eager

@@ -167,10 +167,17 @@ int  ddpm_comm_error(const ddpm_comm* c, int* h_err);
 void ddpm_comm_destroy(ddpm_comm* c);
 /* Same arguments as ddpm_train_steps_persistent minus d_grads/grad_scale (the bucket is the
  * communicator's; gradients are scaled by 1/world).  d_loss reports THIS rank's batch loss, as the
- * reference's per-rank `batch_loss` does (mp:461). */
+ * reference's per-rank `batch_loss` does (mp:461).
+ *   d_idx      i64[nsteps*batch]: this rank's batches (may be NULL when d_idx_all is given)
+ *   d_idx_all  i64[world][idx_stride], row r = rank r's batches of this launch (DistributedSampler shards are a
+ *              pure function of (seed, epoch, rank), so every rank can compute all of them), or NULL.
+ *              When given and batch <= 64, fc1's gradient (85 % of the bucket) is not exchanged at all: ranks
+ *              exchange their dz1 rows (32 KB) and each forms the global-batch dW1 tile itself from the
+ *              resident dataset — same sums in the same (rank) order on every rank. */
 int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,
                                const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
-                               const int64_t* d_idx, const uint8_t* d_masks,
+                               const int64_t* d_idx, const int64_t* d_idx_all, int64_t idx_stride,
+                               const uint8_t* d_masks,
                                uint64_t philox_seed, uint64_t philox_step0,
                                int batch, int nsteps, unsigned flags, float lr,
                                float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);

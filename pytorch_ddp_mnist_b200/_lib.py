@@ -18,7 +18,7 @@ OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
 FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class DDPMError(RuntimeError):
@@ -57,8 +57,8 @@ SIGNATURES = {
     "ddpm_comm_connect": (_i32, [_vp, _vp]),
     "ddpm_comm_error": (_i32, [_vp, C.POINTER(_i32)]),
     "ddpm_comm_destroy": (None, [_vp]),
-    "ddpm_train_steps_fused_ddp": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32, _f32,
-                                          _vp, _vp, _vp, _vp]),
+    "ddpm_train_steps_fused_ddp": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _u64, _u64, _i32, _i32, _u32,
+                                          _f32, _vp, _vp, _vp, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),

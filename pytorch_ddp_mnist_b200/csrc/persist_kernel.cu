@@ -45,6 +45,8 @@ constexpr int CR = 64;                                // batch rows per smem chu
 constexpr int XS_LD = 60;                             // padded row of the decoded pixel tile (16B aligned)
 constexpr int PERSIST_MAX_BATCH = 512;
 #define DDPM_MAX_WORLD 8
+// activation exchange: per (parity, source rank, batch row) 528 eight-byte words
+constexpr int ACT_DZ1 = 0, ACT_DZ2 = 128, ACT_H1D = 256, ACT_H2 = 384, ACT_DZ3 = 512, ACT_ROW_WORDS = 528;
 
 struct PersistArgs {
     float* params; float* grads;
@@ -62,6 +64,13 @@ struct PersistArgs {
     unsigned long long* xrecv[DDPM_MAX_WORLD];        // every rank's receive buffer [2 parities][world sources][NP] of
                                                       // 8-byte (value, step) words, peer-mapped
     int* xerr;                                        // local error word (exchange timeout)
+    // activation exchange (batch <= 64): instead of the 473 KB of gradients, ranks exchange the per-row quantities
+    // the gradients are made of (dz1, dz2, h1d, h2: 128 each, dz3: 16 -> 135 KB per rank) as they are produced in
+    // phase B, and every rank forms the GLOBAL-batch gradient tiles itself, summing sources in rank order (all
+    // ranks hold the whole dataset and know every shard).  Nothing is exchanged after phase C any more.
+    unsigned long long* xrecv_dz[DDPM_MAX_WORLD];     // every rank's buffer [2 parities][world sources][CR rows][ACT_ROW_WORDS]
+    const int64_t* idx_all; size_t idx_stride;        // i64 [world][idx_stride]: every rank's batches of this launch
+    int act_exchange;
 };
 
 struct __align__(16) PersistSmem {
@@ -70,6 +79,7 @@ struct __align__(16) PersistSmem {
     float b1[HID], b2[HID];
     float w1t[NT * MT];                               // [n][m]  owned W1 tile (persistent across steps)
     float xs[2][CR * XS_LD];                          // decoded pixels of the tile, [row][60]; double buffered
+    float xsx[CR * XS_LD];                            // pixel tile of another rank's batch (activation exchange)
     float dzt[CR * MT];                               // dz1 tile [row][16]
     float hs[HID], h2s[HID], ds[HID];                 // row vectors
     float red[2 * HID];
@@ -262,6 +272,60 @@ __device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long
     for (int i = 0; i < N; ++i) v[i] = sum[i];
 }
 
+__device__ __forceinline__ void act_push(const PersistArgs& a, unsigned long long T, int row, int word, float v) {
+    const float one[1] = {v};
+    const size_t slot = (((size_t)(T & 1) * a.world + a.rank) * CR + row) * ACT_ROW_WORDS + word;
+    for (int r = 0; r < a.world; ++r)
+        if (r != a.rank) ll_store<1>(a.xrecv_dz[r] + slot, (unsigned)T, one);
+}
+// dst[r][0..NCOLS) for rows r < CR: from this rank's workspace (src_rank == a.rank) or from the words rank
+// `src_rank` pushed into this rank's buffer (polled until they carry step T); rows >= B are zero.
+template <int NCOLS>
+__device__ __forceinline__ void act_stage(const PersistArgs& a, unsigned long long T, int src_rank, float* dst, int dst_ld,
+                                          const float* local, int local_ld, int col0, int word0) {
+    constexpr int PAIRS = NCOLS / 2, PER_THREAD = CR * PAIRS / P_THREADS;      // 2 (16 columns) or 4 (32 columns)
+    static_assert(CR * PAIRS % P_THREADS == 0, "tile must divide evenly");
+    const unsigned long long* base =
+        a.xrecv_dz[a.rank] + (((size_t)(T & 1) * a.world + src_rank) * CR) * ACT_ROW_WORDS + word0 + col0;
+    const unsigned t32 = (unsigned)T;
+    float2 v[PER_THREAD];
+    if (src_rank == a.rank) {
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
+            v[i] = r < a.B ? __ldcg(reinterpret_cast<const float2*>(local + (size_t)r * local_ld + col0 + c2))
+                           : make_float2(0.f, 0.f);
+        }
+    } else {
+        // first round: every poll of this thread in flight at once; then re-poll only what has not arrived
+        unsigned x0[PER_THREAD], f0[PER_THREAD], x1[PER_THREAD], f1[PER_THREAD];
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
+            x0[i] = x1[i] = 0u; f0[i] = f1[i] = t32;
+            if (r < a.B)
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0[i]), "=r"(f0[i]), "=r"(x1[i]), "=r"(f1[i])
+                             : "l"(base + (size_t)r * ACT_ROW_WORDS + c2) : "memory");
+        }
+        const long long t0 = clock64();
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
+            while (f0[i] != t32 || f1[i] != t32) {
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0[i]), "=r"(f0[i]), "=r"(x1[i]), "=r"(f1[i])
+                             : "l"(base + (size_t)r * ACT_ROW_WORDS + c2) : "memory");
+                if ((f0[i] != t32 || f1[i] != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
+            }
+            v[i] = make_float2(__uint_as_float(x0[i]), __uint_as_float(x1[i]));
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < PER_THREAD; ++i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
+        *reinterpret_cast<float2*>(&dst[r * dst_ld + c2]) = v[i];
+    }
+}
+
 __global__ void __launch_bounds__(P_THREADS, 1)
 train_persist_kernel(PersistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -308,6 +372,8 @@ train_persist_kernel(PersistArgs a) {
         float* xs_cur = s.xs[step & 1];
         const bool prefetch = own_w1 && single && (step + 1 < a.nsteps);
         const bool ddp = a.world > 1;
+        const bool actx = ddp && a.act_exchange && single;           // W1 through the dz1 exchange
+        const bool actx_all = actx && a.act_exchange == 2;           // ... and W2 / W3 / biases through dz2, h1d, h2, dz3
         const unsigned long long T = a.comm_step + step + 1;            // global step number of this communicator
 
         // ================================ phase A ================================
@@ -422,6 +488,7 @@ train_persist_kernel(PersistArgs a) {
                     const float z = (s.red[j] + s.red[HID + j]) + s.b1[j];
                     h1 = (z > 0.f && keep) ? z * scale : 0.f;
                     a.h1d[(size_t)row * HID + j] = h1;
+                    if (actx_all) act_push(a, T, row, ACT_H1D + j, h1);
                     s.hs[j] = h1;
                 }
                 __syncthreads();
@@ -451,6 +518,7 @@ train_persist_kernel(PersistArgs a) {
                     gate2 = z2 > 0.f;
                     const float hv = gate2 ? z2 : 0.f;
                     a.h2[(size_t)row * HID + j] = hv;
+                    if (actx_all) act_push(a, T, row, ACT_H2 + j, hv);
                     s.h2s[j] = hv;
                 }
                 __syncthreads();
@@ -491,6 +559,7 @@ train_persist_kernel(PersistArgs a) {
                         const float d = lane < NC ? (e / sum - (lane == yv ? 1.f : 0.f)) * invB : 0.f;
                         s.dzs[lane] = d;
                         a.dz3[(size_t)row * NCP + lane] = d;
+                        if (actx_all) act_push(a, T, row, ACT_DZ3 + lane, d);
                     }
                 }
                 __syncthreads();
@@ -502,6 +571,7 @@ train_persist_kernel(PersistArgs a) {
                     for (int c = 0; c < NC; ++c) d = fmaf(s.dzs[c], s.w3[c * HID + j], d);
                     d = gate2 ? d : 0.f;
                     a.dz2[(size_t)row * HID + j] = d;
+                    if (actx_all) act_push(a, T, row, ACT_DZ2 + j, d);
                     s.ds[j] = d;
                 }
                 __syncthreads();
@@ -526,7 +596,9 @@ train_persist_kernel(PersistArgs a) {
                     float v = 0.f;
 #pragma unroll
                     for (int q = 0; q < 16; ++q) v += red2[q * RLD + j];
-                    a.dz1[(size_t)row * HID + j] = (h1 > 0.f) ? v * scale : 0.f;
+                    const float dzv = (h1 > 0.f) ? v * scale : 0.f;
+                    a.dz1[(size_t)row * HID + j] = dzv;
+                    if (actx) act_push(a, T, row, ACT_DZ1 + j, dzv);
                 }
                 __syncthreads();
             }
@@ -548,14 +620,32 @@ train_persist_kernel(PersistArgs a) {
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int jx = 0; jx < 4; ++jx) acc[i][jx] = 0.f;
-            for (int c = 0; c < nchunks; ++c) {
+            // activation-exchange mode: one pass per SOURCE RANK, in rank order on every rank (identical sums);
+            // the next remote source's pixel tile is fetched while the current one is being multiplied
+            const int npass = actx ? a.world : nchunks;
+            int nxt = -1;
+            if (actx) {
+                nxt = (a.rank == 0) ? 1 : 0;
+                tile_load(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
+            }
+            for (int c = 0; c < npass; ++c) {
                 __syncthreads();
-                if (!single) { tile_load(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
-                {
+                const float* xs_src = xs_cur;
+                if (!actx) {
+                    if (!single) { tile_load(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
+                } else if (c != a.rank) {
+                    tile_store(px, s, s.xsx);
+                    xs_src = s.xsx;
+                    nxt = c + 1 + ((c + 1 == a.rank) ? 1 : 0);
+                    if (nxt < a.world) tile_load(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
+                }
+                if (!actx) {
                     const int r = tid >> 2, q = tid & 3, row = c * CR + r;      // 64 rows x 4 float4
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (row < B) v = __ldcg(reinterpret_cast<const float4*>(a.dz1 + (size_t)row * HID + mt * MT) + q);
                     *reinterpret_cast<float4*>(&s.dzt[r * MT + q * 4]) = v;
+                } else {
+                    act_stage<MT>(a, T, c, s.dzt, MT, a.dz1, HID, mt * MT, ACT_DZ1);   // rank c's dz1 rows, this tile's columns
                 }
                 __syncthreads();
                 DBG_STAMP(9);
@@ -574,7 +664,7 @@ train_persist_kernel(PersistArgs a) {
                     for (int rr = 0; rr < CR / 4; ++rr) {
                         const int r = qd * (CR / 4) + rr;
                         const float4 d = *reinterpret_cast<const float4*>(&s.dzt[r * MT + mq * 4]);
-                        const float4 x = *reinterpret_cast<const float4*>(&xs_cur[r * XS_LD + n4 * 4]);
+                        const float4 x = *reinterpret_cast<const float4*>(&xs_src[r * XS_LD + n4 * 4]);
                         const float dv[4] = {d.x, d.y, d.z, d.w}, xv[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
@@ -587,7 +677,7 @@ train_persist_kernel(PersistArgs a) {
                 const int offb = DDPM_OFF_B1 + mt * MT + (tid - 224);
                 float gb[1] = {db_acc * a.gscale};
                 const float pold = __ldcg(a.params + offb);
-                if (ddp) ll_allreduce<1>(a, T, cta, offb, gb);
+                if (ddp && !actx) ll_allreduce<1>(a, T, cta, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pold);
             }
             float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
@@ -610,7 +700,7 @@ train_persist_kernel(PersistArgs a) {
                 g[2] = ((p[0].z + p[1].z) + (p[2].z + p[3].z)) * a.gscale;
                 g[3] = ((p[0].w + p[1].w) + (p[2].w + p[3].w)) * a.gscale;
                 const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
-                if (ddp) {                                      // push to every peer, then sum everyone's tile
+                if (ddp && !actx) {                             // push to every peer, then sum everyone's tile
                     DBG_STAMP(11);
                     ll_allreduce<4>(a, T, cta, off, g);
                     DBG_STAMP(12);
@@ -637,9 +727,12 @@ train_persist_kernel(PersistArgs a) {
             const float pbias = do_db ? __ldcg(a.params + DDPM_OFF_B2 + jt * 16 + tid) : 0.f;
             float acc[4][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
             float db_acc = 0.f;
-            for (int c = 0; c < nchunks; ++c) {
+            for (int c = 0; c < (actx_all ? a.world : nchunks); ++c) {   // actx_all: one pass per source rank, in rank order
                 __syncthreads();
-                {
+                if (actx_all) {
+                    act_stage<MT>(a, T, c, s.dzt, MT, a.dz2, HID, jt * 16, ACT_DZ2);
+                    act_stage<32>(a, T, c, hst, 32, a.h1d, HID, kt * 32, ACT_H1D);
+                } else {
                     const int r = tid >> 2, q = tid & 3, row = c * CR + r;
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f), u0 = v, u1 = v;
                     if (row < B) {
@@ -682,14 +775,14 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
                 float g[2] = {((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale,
                               ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale};
-                if (ddp) ll_allreduce<2>(a, T, cta, off, g);
+                if (ddp && !actx_all) ll_allreduce<2>(a, T, cta, off, g);
                 grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
                 grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
             }
             if (do_db) {
                 const int offb = DDPM_OFF_B2 + jt * 16 + tid;
                 float gb[1] = {db_acc * a.gscale};
-                if (ddp) ll_allreduce<1>(a, T, cta, offb, gb);
+                if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
             }
         } else {
@@ -709,9 +802,12 @@ train_persist_kernel(PersistArgs a) {
             float acc[NC];
 #pragma unroll
             for (int i = 0; i < NC; ++i) acc[i] = 0.f;
-            for (int c = 0; c < nchunks; ++c) {
+            for (int c = 0; c < (actx_all ? a.world : nchunks); ++c) {
                 __syncthreads();
-                {
+                if (actx_all) {
+                    act_stage<NCP>(a, T, c, s.dzt, MT, a.dz3, NCP, 0, ACT_DZ3);
+                    act_stage<32>(a, T, c, hst, 32, a.h2, HID, kt * 32, ACT_H2);
+                } else {
                     const int r = tid >> 2, q = tid & 3, row = c * CR + r;
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f), u0 = v, u1 = v;
                     if (row < B) {
@@ -747,13 +843,13 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
                 const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
                 float ga[1] = {g0 * a.gscale};
-                if (ddp) ll_allreduce<1>(a, T, cta, o0, ga);
+                if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, o0, ga);
                 grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) {
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
                     float gc[1] = {g1 * a.gscale};
-                    if (ddp) ll_allreduce<1>(a, T, cta, o1, gc);
+                    if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, o1, gc);
                     grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
                 }
             }
@@ -879,7 +975,7 @@ extern "C" int ddpm_train_steps_persistent(
 struct ddpm_comm {
     int rank = 0, world = 1, device = 0;
     void* local = nullptr;                       // cudaMalloc'd: receive buffer [2][world][NP] x 8 B | i32 error
-    size_t recv_bytes = 0;
+    size_t recv_bytes = 0, dz_bytes = 0;         // gradient words | dz1 words (activation exchange)
     void* peer[DDPM_MAX_WORLD] = {};             // peer[r]: rank r's buffer in this process's address space
     bool opened[DDPM_MAX_WORLD] = {};
     unsigned long long steps = 0;                // fused steps run so far (same on every rank)
@@ -900,9 +996,10 @@ extern "C" int ddpm_comm_create(int rank, int world, ddpm_comm** out) {
     }
     DDPM_CUDA(cudaGetDevice(&c->device));
     c->recv_bytes = 2 * (size_t)world * NP * sizeof(unsigned long long);     // 15 MB at world 8
-    cudaError_t e = cudaMalloc(&c->local, c->recv_bytes + 256);
+    c->dz_bytes = 2 * (size_t)world * CR * ACT_ROW_WORDS * sizeof(unsigned long long);      // 4.3 MB at world 8
+    cudaError_t e = cudaMalloc(&c->local, c->recv_bytes + c->dz_bytes + 256);
     if (e != cudaSuccess) { delete c; return set_error("ddpm_comm_create: cudaMalloc failed: %s", cudaGetErrorString(e)); }
-    e = cudaMemset(c->local, 0, c->recv_bytes + 256);       // step field 0 never matches a real step (steps start at 1)
+    e = cudaMemset(c->local, 0, c->recv_bytes + c->dz_bytes + 256);   // step field 0 never matches a real step (steps start at 1)
     if (e != cudaSuccess) { cudaFree(c->local); delete c; return set_error("ddpm_comm_create: cudaMemset failed: %s", cudaGetErrorString(e)); }
     c->peer[rank] = c->local;
     *out = c;
@@ -933,7 +1030,7 @@ extern "C" int ddpm_comm_connect(ddpm_comm* c, const void* h_handles) {
 
 extern "C" int ddpm_comm_error(const ddpm_comm* c, int* h_err) {
     DDPM_CHECK_ARG(c && h_err, "ddpm_comm_error: null argument");
-    DDPM_CUDA(cudaMemcpy(h_err, (char*)c->local + c->recv_bytes, sizeof(int), cudaMemcpyDeviceToHost));
+    DDPM_CUDA(cudaMemcpy(h_err, (char*)c->local + c->recv_bytes + c->dz_bytes, sizeof(int), cudaMemcpyDeviceToHost));
     return 0;
 }
 
@@ -948,10 +1045,13 @@ extern "C" void ddpm_comm_destroy(ddpm_comm* c) {
 extern "C" int ddpm_train_steps_fused_ddp(
         ddpm_comm* comm, float* d_params,
         const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
-        const int64_t* d_idx, const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
+        const int64_t* d_idx, const int64_t* d_idx_all, int64_t idx_stride,
+        const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
         int batch, int nsteps, unsigned flags, float lr,
         float* d_loss, float* d_loss_steps, void* d_workspace, void* stream) {
     DDPM_CHECK_ARG(comm != nullptr, "ddpm_train_steps_fused_ddp: null communicator");
+    DDPM_CHECK_ARG(d_idx_all == nullptr || idx_stride >= (int64_t)nsteps * batch,
+                   "ddpm_train_steps_fused_ddp: idx_stride %lld shorter than nsteps*batch", (long long)idx_stride);
     DDPM_CHECK_ARG(lr != 0.f, "ddpm_train_steps_fused_ddp: lr must be non-zero (the update is part of the exchange)");
     for (int r = 0; r < comm->world; ++r)
         DDPM_CHECK_ARG(comm->peer[r] != nullptr, "ddpm_train_steps_fused_ddp: rank %d is not connected (ddpm_comm_connect)", r);
@@ -959,8 +1059,16 @@ extern "C" int ddpm_train_steps_fused_ddp(
     memset(&a, 0, sizeof(a));
     a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
     a.two_stage = comm->two_stage;
-    for (int r = 0; r < comm->world; ++r) a.xrecv[r] = (unsigned long long*)comm->peer[r];
-    a.xerr = (int*)((char*)comm->local + comm->recv_bytes);
+    for (int r = 0; r < comm->world; ++r) {
+        a.xrecv[r] = (unsigned long long*)comm->peer[r];
+        a.xrecv_dz[r] = (unsigned long long*)((char*)comm->peer[r] + comm->recv_bytes);
+    }
+    a.xerr = (int*)((char*)comm->local + comm->recv_bytes + comm->dz_bytes);
+    // fc1's gradient through the dz1 exchange when every rank's indices are known and the batch is one chunk
+    a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
+    if (a.act_exchange && getenv("DDPM_ACT_EXCHANGE_ALL") != nullptr) a.act_exchange = 2;   // also W2 / W3 / biases (measured slower at ws = 2)
+    a.idx_all = d_idx_all; a.idx_stride = (size_t)idx_stride;
+    if (d_idx == nullptr && d_idx_all != nullptr) d_idx = d_idx_all + (size_t)comm->rank * idx_stride;
     const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,
                                            philox_seed, philox_step0, batch, nsteps, flags, 1.0f / (float)comm->world, lr,
                                            d_loss, d_loss_steps, d_workspace, stream, "ddpm_train_steps_fused_ddp");

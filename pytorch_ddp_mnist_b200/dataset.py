@@ -209,6 +209,20 @@ class DeviceBatchLoader:
         flat = torch.cat(batches).to(self.resident.device, non_blocking=True)
         return flat, [len(b) for b in batches]
 
+    def epoch_indices_all_ranks(self, epoch: int) -> Optional[torch.Tensor]:
+        """i64[world, samples_per_rank] on the device: every rank's shard of `epoch` (DistributedSampler is a pure
+        function of (seed, epoch, rank)); None when the sampler is not a DistributedSampler."""
+        smp = self._index_loader.sampler
+        if not isinstance(smp, DistributedSampler):
+            return None
+        rows = []
+        for r in range(smp.num_replicas):
+            sr = DistributedSampler(_IndexOnly(len(self.resident)), num_replicas=smp.num_replicas, rank=r,
+                                    shuffle=smp.shuffle, seed=smp.seed, drop_last=smp.drop_last)
+            sr.set_epoch(epoch)
+            rows.append(torch.tensor(list(iter(sr)), dtype=torch.int64))
+        return torch.stack(rows).to(self.resident.device)
+
     def index_batches(self) -> Iterator[torch.Tensor]:
         """The epoch's batches as int64 index tensors on the device."""
         flat, sizes = self.epoch_indices()

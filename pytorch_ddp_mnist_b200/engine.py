@@ -118,11 +118,12 @@ class TrainEngine:
 
     def train_steps(self, resident, idx_flat: torch.Tensor, batch: int, nsteps: int,
                     masks: Optional[torch.Tensor] = None, philox_step0: Optional[int] = None,
-                    loss_steps: Optional[torch.Tensor] = None) -> None:
+                    loss_steps: Optional[torch.Tensor] = None, idx_all: Optional[torch.Tensor] = None) -> None:
         """`nsteps` consecutive optimisation steps over `idx_flat` (i64[nsteps*batch], device).
         batch <= 512: the persistent kernel — ONE launch for all steps at ws == 1; at ws > 1 one
         launch per step writes the pre-divided bucket, then allreduce + flat SGD.  Larger batches
-        fall back to the three-kernel step."""
+        fall back to the three-kernel step.  `idx_all` i64[world, nsteps*batch] (every rank's batches, row
+        `rank` == idx_flat) lets the fused kernel replace fc1's gradient exchange by the dz1 exchange."""
         from ._lib import PERSIST_MAX_BATCH
         st0 = self.step_count if philox_step0 is None else philox_step0
         self.step_count += nsteps
@@ -140,8 +141,8 @@ class TrainEngine:
             return
         if self.comm is not None:
             mk = dict(masks=masks) if masks is not None else dict(philox=(self.seed, st0))
-            ops.train_steps_fused_ddp(self.comm, self.params, self.ws, batch, nsteps, idx=idx_flat, lr=self.lr,
-                                      loss=self.loss, loss_steps=loss_steps, **mk, **kw)
+            ops.train_steps_fused_ddp(self.comm, self.params, self.ws, batch, nsteps, idx=idx_flat, idx_all=idx_all,
+                                      lr=self.lr, loss=self.loss, loss_steps=loss_steps, **mk, **kw)
             return
         import torch.distributed as dist
         for t in range(nsteps):

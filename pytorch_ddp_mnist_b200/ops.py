@@ -206,11 +206,13 @@ class FusedComm:
 
 def train_steps_fused_ddp(comm: FusedComm, params: torch.Tensor, ws: Workspace, batch: int, nsteps: int, *,
                           images: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor,
+                          idx_all: Optional[torch.Tensor] = None,
                           masks: Optional[torch.Tensor] = None, philox: Optional[Tuple[int, int]] = None,
                           lr: float, loss: Optional[torch.Tensor] = None,
                           loss_steps: Optional[torch.Tensor] = None) -> None:
     """`nsteps` data-parallel optimisation steps in one launch per rank; the gradient average and
-    the update happen inside the kernel over NVLink peer memory."""
+    the update happen inside the kernel over NVLink peer memory.  `idx_all` i64[world, >= nsteps*batch]
+    (every rank's batches) enables the dz1 exchange for fc1 when batch <= 64."""
     _need(params, "params", torch.float32, (N_PARAMS,))
     if batch > ws.max_batch:
         raise ValueError(f"batch {batch} exceeds workspace max_batch {ws.max_batch}")
@@ -225,9 +227,15 @@ def train_steps_fused_ddp(comm: FusedComm, params: torch.Tensor, ws: Workspace, 
     _need(loss_steps, "loss_steps", torch.float32, optional=True)
     seed, step0 = philox if philox else (0, 0)
     flags = _lib.FWD_PHILOX_MASK if philox else 0
-    check(lib.ddpm_train_steps_fused_ddp(comm._h, ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(masks),
-                                         seed, step0, batch, nsteps, flags, lr, ptr(loss), ptr(loss_steps),
-                                         ptr(ws.buf), cur_stream()))
+    stride = 0
+    if idx_all is not None:
+        _need(idx_all, "idx_all", torch.int64)
+        if idx_all.dim() != 2 or idx_all.shape[0] != comm.world or idx_all.shape[1] < nsteps * batch:
+            raise ValueError("idx_all must be i64[world, >= nsteps*batch]")
+        stride = idx_all.shape[1]
+    check(lib.ddpm_train_steps_fused_ddp(comm._h, ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(idx_all),
+                                         stride, ptr(masks), seed, step0, batch, nsteps, flags, lr, ptr(loss),
+                                         ptr(loss_steps), ptr(ws.buf), cur_stream()))
 
 
 def cross_entropy(logits: torch.Tensor, y: torch.Tensor, loss: Optional[torch.Tensor] = None,

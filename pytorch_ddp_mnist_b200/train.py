@@ -130,6 +130,7 @@ def main(model: nn.Module, train_loader: DeviceBatchLoader, test_loader: DeviceB
         train_loader.sampler.set_epoch(i)                # mp:449
         eng.zero_epoch_loss()
         flat, sizes = train_loader.epoch_indices()
+        all_ranks = train_loader.epoch_indices_all_ranks(i) if eng.comm is not None else None
         # consecutive equal-sized batches go to the device as ONE launch of the persistent kernel
         # (`progress` splits the epoch into chunks so a loss can be shown); the short last batch is its own launch
         pos, n = 0, 0
@@ -142,7 +143,8 @@ def main(model: nn.Module, train_loader: DeviceBatchLoader, test_loader: DeviceB
             masks = None
             if mask_fn is not None:
                 masks = torch.stack([mask_fn(step_no + t, b) for t in range(k)]).to(device, torch.uint8).contiguous()
-            eng.train_steps(train_res, flat[pos:pos + k * b], b, k, masks=masks)
+            ia = all_ranks[:, pos:pos + k * b].contiguous() if all_ranks is not None else None
+            eng.train_steps(train_res, flat[pos:pos + k * b], b, k, masks=masks, idx_all=ia)
             step_no += k
             pos += k * b
             n = m

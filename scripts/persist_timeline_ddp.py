@@ -21,11 +21,13 @@ eng.enable_fused_ddp()
 idx = torch.randperm(60000, device=dev)[:40 * B].to(torch.int64)
 G = 148
 dbg = torch.zeros(G * 8 * 16, dtype=torch.int64, device=dev)
-eng.train_steps(res, idx[:20 * B], B, 20)
+ia = torch.stack([idx.roll(r * 7) for r in range(world)])  # every rank passes the same table; row `rank` is its own
+idx_r = ia[rank].contiguous()
+eng.train_steps(res, idx_r[:20 * B], B, 20, idx_all=ia[:, :20 * B].contiguous())
 torch.cuda.synchronize(); dist.barrier()
 _lib.lib.ddpm_debug_set_persist_timing.argtypes = [C.c_void_p]
 _lib.lib.ddpm_debug_set_persist_timing(dbg.data_ptr())
-eng.train_steps(res, idx[20 * B:], B, 20)
+eng.train_steps(res, idx_r[20 * B:], B, 20, idx_all=ia[:, 20 * B:].contiguous())
 torch.cuda.synchronize()
 _lib.lib.ddpm_debug_set_persist_timing(None)
 eng.check_comm()
@@ -38,6 +40,6 @@ if rank == 0:
         print(f"cta {cta:3d}: " + " ".join(f"{n}={int(v):6d}" for n, v in zip(names, seg)) + f"  step={int(tot)}")
     for cta in (0, 100):
         x = d[cta, 2:8]
-        print(f"cta {cta} phase C: compute+send={int((x[:,11]-x[:,4]).mean())} reduce-wait={int((x[:,12]-x[:,11]).mean())} update={int((x[:,5]-x[:,12]).mean())}")
+        print(f"cta {cta} phase B: partials+wait={int((x[:,6]-x[:,2]).mean())} z2={int((x[:,7]-x[:,6]).mean())} logits+softmax={int((x[:,8]-x[:,7]).mean())} dz2+dz1={int((x[:,3]-x[:,8]).mean())}")
 dist.barrier()
 os._exit(0)

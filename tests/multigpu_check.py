@@ -69,7 +69,16 @@ def main():
     eng2.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
     eng2.enable_fused_ddp()
     ls = torch.zeros(idx.shape[0], device=dev)
-    eng2.train_steps(res, idx.reshape(-1).contiguous(), 64, idx.shape[0], masks=masks.contiguous(), loss_steps=ls)
+    # every rank's batches: fc1's gradient then goes through the dz1 exchange (DDPM_NO_ACT_EXCHANGE=1 keeps the
+    # full gradient exchange; both are exercised by the callers of this script)
+    if golden_ws:
+        all_np = np.stack([g[f"rank{r}.idx"].reshape(-1) for r in range(world)])
+    else:
+        all_np = np.stack([O.shard_indices(60000, world, r)[:20 * 64] for r in range(world)])
+    idx_all = torch.from_numpy(np.ascontiguousarray(all_np)).to(dev)
+    assert torch.equal(idx_all[rank], idx.reshape(-1))
+    eng2.train_steps(res, idx.reshape(-1).contiguous(), 64, idx.shape[0], masks=masks.contiguous(), loss_steps=ls,
+                     idx_all=idx_all)
     torch.cuda.synchronize()
     eng2.check_comm()
     l2 = ls.cpu().numpy()
@@ -82,7 +91,7 @@ def main():
     dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "fused replicas diverged"
     # a second launch continues the flag sequence (communicator step counter) and stays in lock-step
-    eng2.train_steps(res, idx[:4].reshape(-1).contiguous(), 64, 4)
+    eng2.train_steps(res, idx[:4].reshape(-1).contiguous(), 64, 4, idx_all=idx_all[:, :4 * 64].contiguous())
     torch.cuda.synchronize()
     eng2.check_comm()
     mine = eng2.params.clone()
@@ -91,8 +100,9 @@ def main():
     assert torch.equal(mine, other), "fused replicas diverged after the second launch"
     dist.barrier()
     if rank == 0:
-        print("MULTIGPU_OK world %d exchange %s max loss err %.2e fused-vs-nccl %.2e" %
-              (world, os.environ.get("DDPM_EXCHANGE", "default"), err, rel))
+        print("MULTIGPU_OK world %d exchange %s act_exchange %s max loss err %.2e fused-vs-nccl %.2e" %
+              (world, os.environ.get("DDPM_EXCHANGE", "default"), "off" if os.environ.get("DDPM_NO_ACT_EXCHANGE") else "on",
+               err, rel))
     dist.destroy_process_group()
 
 

@@ -31,7 +31,7 @@ def test_header_symbols_all_exported_and_bound(L):
     assert declared == set(L.SIGNATURES), declared ^ set(L.SIGNATURES)
     for name in declared:
         assert hasattr(L.lib, name), name
-    assert L.lib.ddpm_abi_version() == 1
+    assert L.lib.ddpm_abi_version() == L.ABI_VERSION
 
 
 def test_layout_constants_match_header(L):
