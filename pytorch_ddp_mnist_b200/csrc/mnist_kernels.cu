@@ -35,7 +35,7 @@ constexpr int G1_LARGE_BATCH = 1024;
 constexpr int TARGET_ITEMS = 296;                 // 2 x 148 SMs
 
 // grads_kernel cuts large batches into slices so that more than 67 CTAs have work
-int grads_bsplit(int batch) { return batch >= 1024 ? (batch / 256 < 16 ? batch / 256 : 16) : 1; }
+int grads_bsplit(int batch) { return batch >= 1024 ? (batch / 128 < 32 ? batch / 128 : 32) : 1; }
 
 int fc1_ksplit(int batch) {
     const bool large = batch >= G1_LARGE_BATCH;
@@ -495,6 +495,277 @@ rows_kernel(RowsArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------
+// ROWS for large batches: the same per-row chain as rows_kernel, organised as small GEMMs.
+// 256 threads handle 32 batch rows per pass; thread (rg, cg) owns the 4x4 block rows 4rg.., units 4cg..
+// of every [32 x 128] intermediate.  W2 sits in shared memory twice (row-major for dz2.W2, transposed
+// for h1d.W2^T) so that both products read one broadcast LDS.128 (4 rows of the k-major activation
+// tile) and one conflict-free LDS.128 (4 weights) per 16 FMAs.  Exact fp32, fixed summation order.
+// ------------------------------------------------------------------------------------------
+constexpr int RG_ROWS = 32;                       // batch rows per pass
+constexpr int RG_LD = RG_ROWS + 4;                // k-major activation tiles [128][36]: float4 rows, conflict-free stores
+
+struct RowsGemmSmem {
+    float w2[HID * HID];                          // W2[j][k]
+    float w2t[HID * HID];                         // W2^T[k][j]
+    float w3[NC * HID];
+    float b1[HID], b2[HID];
+    float aT[HID * RG_LD];                        // h1d^T  [k][row]
+    float hT[HID * RG_LD];                        // h2^T   [j][row]
+    float dT[HID * RG_LD];                        // dz2^T  [j][row]
+    float z3[RG_ROWS * NCP];                      // logits
+    float d3[RG_ROWS * NCP];                      // dlogits (zero padded)
+    float red[256];
+    int last;
+};
+
+// W2^T is stored with its 16-byte column chunks XOR-swizzled by (k / 4): the transposing stores of the staging
+// loop (32 lanes, same j, k = 4*lane + i) then spread over the banks instead of hitting one (32-way conflict)
+__device__ __forceinline__ int w2t_idx(int k, int j) { return k * HID + ((((j >> 2) ^ (k >> 2)) & 31) << 2) + (j & 3); }
+
+template <bool SWZ>
+__device__ __forceinline__ void rg_mma(const float* __restrict__ actT, const float* __restrict__ w, int rg, int cg,
+                                       float (&acc)[4][4]) {
+    // acc[r][c] += sum_k actT[k][4rg + r] * w[k][4cg + c]
+#pragma unroll 8
+    for (int k = 0; k < HID; ++k) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&actT[k * RG_LD + rg * 4]);
+        const float4 w4 = *reinterpret_cast<const float4*>(&w[SWZ ? w2t_idx(k, cg * 4) : k * HID + cg * 4]);
+        const float av[4] = {a4.x, a4.y, a4.z, a4.w}, wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[r][c] = fmaf(av[r], wv[c], acc[r][c]);
+    }
+}
+
+__global__ void __launch_bounds__(256, 1)
+rows_gemm_kernel(RowsArgs a) {
+    extern __shared__ __align__(16) unsigned char rg_smem_raw[];
+    RowsGemmSmem& s = *reinterpret_cast<RowsGemmSmem*>(rg_smem_raw);
+    const int tid = threadIdx.x, rg = tid >> 5, cg = tid & 31;
+    const float* W2 = a.params + DDPM_OFF_W2;
+    for (int t = tid; t < HID * HID / 4; t += 256) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(W2) + t);
+        *reinterpret_cast<float4*>(&s.w2[t * 4]) = v;
+        const int j = t >> 5, k = (t & 31) * 4;
+        s.w2t[w2t_idx(k + 0, j)] = v.x; s.w2t[w2t_idx(k + 1, j)] = v.y;
+        s.w2t[w2t_idx(k + 2, j)] = v.z; s.w2t[w2t_idx(k + 3, j)] = v.w;
+    }
+    for (int t = tid; t < NC * HID; t += 256) s.w3[t] = __ldg(a.params + DDPM_OFF_W3 + t);
+    if (tid < HID) { s.b1[tid] = __ldg(a.params + DDPM_OFF_B1 + tid); s.b2[tid] = __ldg(a.params + DDPM_OFF_B2 + tid); }
+    const bool prep_bwd = (a.flags & DDPM_FWD_PREP_BACKWARD) != 0;
+    const bool philox = (a.flags & DDPM_FWD_PHILOX_MASK) != 0;
+    const bool train = philox || a.mask != nullptr;
+    if (blockIdx.x == 0 && tid == 0) a.ctrl[1] = train ? 1u : 0u;
+    const bool have_y = a.y != nullptr || (a.labels != nullptr && a.idx != nullptr);
+    const float scale = train ? 1.25f : 1.0f;
+    const int B = a.B;
+    const float invB = 1.0f / (float)B;
+    __syncthreads();
+
+    for (int row0 = blockIdx.x * RG_ROWS; row0 < B; row0 += gridDim.x * RG_ROWS) {
+        // ---- 1. z1 = sum of split-K partials + b1 ; ReLU ; dropout  -> h1 (registers), aT (smem), h1d (global)
+        float h1[4][4];
+        {
+            const float4 bb = *reinterpret_cast<const float4*>(&s.b1[cg * 4]);
+            const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int row = row0 + rg * 4 + r;
+                float z[4] = {0.f, 0.f, 0.f, 0.f};
+                if (row < B) {
+                    for (int sp = 0; sp < a.ksplit; ++sp) {
+                        const float4 p = __ldcg(reinterpret_cast<const float4*>(a.part + ((size_t)sp * B + row) * HID) + cg);
+                        z[0] += p.x; z[1] += p.y; z[2] += p.z; z[3] += p.w;
+                    }
+                }
+                uchar4 mk = make_uchar4(1, 1, 1, 1);
+                if (row < B && a.mask && !philox) mk = *reinterpret_cast<const uchar4*>(a.mask + (size_t)row * HID + cg * 4);
+                const unsigned char mv[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float zz = z[c] + bv[c];
+                    bool keep = mv[c] != 0;
+                    if (philox) keep = philox_keep(a.seed, a.step, (uint32_t)(row * HID + cg * 4 + c));
+                    h1[r][c] = (row < B && zz > 0.f && keep) ? zz * scale : 0.f;
+                }
+                if (prep_bwd && row < B)
+                    *reinterpret_cast<float4*>(a.h1d + (size_t)row * HID + cg * 4) = make_float4(h1[r][0], h1[r][1], h1[r][2], h1[r][3]);
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<float4*>(&s.aT[(cg * 4 + c) * RG_LD + rg * 4]) = make_float4(h1[0][c], h1[1][c], h1[2][c], h1[3][c]);
+        }
+        __syncthreads();
+        // ---- 2. z2 = h1d . W2^T + b2 ; ReLU -> gate2 (registers), hT (smem), h2 (global)
+        bool gate2[4][4];
+        {
+            float acc[4][4];
+            const float4 bb = *reinterpret_cast<const float4*>(&s.b2[cg * 4]);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) { acc[r][0] = bb.x; acc[r][1] = bb.y; acc[r][2] = bb.z; acc[r][3] = bb.w; }
+            rg_mma<true>(s.aT, s.w2t, rg, cg, acc);
+            float hv[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { gate2[r][c] = acc[r][c] > 0.f; hv[r][c] = gate2[r][c] ? acc[r][c] : 0.f; }
+                const int row = row0 + rg * 4 + r;
+                if (prep_bwd && row < B)
+                    *reinterpret_cast<float4*>(a.h2 + (size_t)row * HID + cg * 4) = make_float4(hv[r][0], hv[r][1], hv[r][2], hv[r][3]);
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<float4*>(&s.hT[(cg * 4 + c) * RG_LD + rg * 4]) = make_float4(hv[0][c], hv[1][c], hv[2][c], hv[3][c]);
+        }
+        __syncthreads();
+        // ---- 3. logits: thread (row = tid & 31, part = tid >> 5) computes classes part and part + 8
+        {
+            const int r = tid & 31, c0 = tid >> 5, c1 = c0 + 8;
+            float v0 = 0.f, v1 = 0.f;
+#pragma unroll 8
+            for (int k = 0; k < HID; ++k) {
+                const float hv = s.hT[k * RG_LD + r];
+                v0 = fmaf(hv, s.w3[c0 * HID + k], v0);
+                if (c1 < NC) v1 = fmaf(hv, s.w3[c1 * HID + k], v1);
+            }
+            s.z3[r * NCP + c0] = v0;
+            if (c1 < NC) s.z3[r * NCP + c1] = v1;
+        }
+        __syncthreads();
+        // ---- 4. log-softmax, NLL, dlogits: one thread per row
+        if (tid < RG_ROWS) {
+            const int row = row0 + tid;
+            float z[NC], m = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) { z[c] = s.z3[tid * NCP + c]; m = fmaxf(m, z[c]); }
+            if (row < B && a.logits) {
+#pragma unroll
+                for (int c = 0; c < NC; ++c) a.logits[(size_t)row * NC + c] = z[c];
+            }
+            float d[NCP];
+#pragma unroll
+            for (int c = 0; c < NCP; ++c) d[c] = 0.f;
+            if (row < B && have_y) {
+                int yv;
+                if (a.y) yv = a.y[row];
+                else {
+                    const int64_t sidx = a.idx[row];
+                    yv = (sidx >= 0 && sidx < a.n_samples) ? a.labels[sidx] : 0;
+                }
+                float e[NC], sum = 0.f;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) { e[c] = expf(z[c] - m); sum += e[c]; }
+                float zy = 0.f;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) zy = (c == yv) ? z[c] : zy;
+                a.rowloss[row] = -((zy - m) - logf(sum));
+                const float inv = 1.0f / sum;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) d[c] = (e[c] * inv - ((c == yv) ? 1.f : 0.f)) * invB;
+                if (prep_bwd) {
+#pragma unroll
+                    for (int c = 0; c < NCP; c += 4)
+                        *reinterpret_cast<float4*>(a.dz3 + (size_t)row * NCP + c) = make_float4(d[c], d[c + 1], d[c + 2], d[c + 3]);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < NCP; ++c) s.d3[tid * NCP + c] = d[c];
+        }
+        __syncthreads();
+        if (prep_bwd && have_y) {
+            // ---- 5. dz2 = (dz3 . W3) * (z2 > 0) -> dT (smem), dz2 (global)
+            float dv[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) dv[r][c] = 0.f;
+#pragma unroll
+            for (int k = 0; k < NC; ++k) {
+                const float4 w4 = *reinterpret_cast<const float4*>(&s.w3[k * HID + cg * 4]);
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const float dd = s.d3[(rg * 4 + r) * NCP + k];
+                    dv[r][0] = fmaf(dd, w4.x, dv[r][0]); dv[r][1] = fmaf(dd, w4.y, dv[r][1]);
+                    dv[r][2] = fmaf(dd, w4.z, dv[r][2]); dv[r][3] = fmaf(dd, w4.w, dv[r][3]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) dv[r][c] = gate2[r][c] ? dv[r][c] : 0.f;
+                const int row = row0 + rg * 4 + r;
+                if (row < B)
+                    *reinterpret_cast<float4*>(a.dz2 + (size_t)row * HID + cg * 4) = make_float4(dv[r][0], dv[r][1], dv[r][2], dv[r][3]);
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<float4*>(&s.dT[(cg * 4 + c) * RG_LD + rg * 4]) = make_float4(dv[0][c], dv[1][c], dv[2][c], dv[3][c]);
+            __syncthreads();
+            // ---- 6. dz1 = (dz2 . W2) * dropout scale * (z1 > 0 && kept)
+            float acc[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r][c] = 0.f;
+            rg_mma<false>(s.dT, s.w2, rg, cg, acc);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int row = row0 + rg * 4 + r;
+                if (row < B)
+                    *reinterpret_cast<float4*>(a.dz1 + (size_t)row * HID + cg * 4) =
+                        make_float4(h1[r][0] > 0.f ? acc[r][0] * scale : 0.f, h1[r][1] > 0.f ? acc[r][1] * scale : 0.f,
+                                    h1[r][2] > 0.f ? acc[r][2] * scale : 0.f, h1[r][3] > 0.f ? acc[r][3] * scale : 0.f);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- batch loss: the last block to finish sums the per-row losses in a fixed order
+    if (have_y && a.loss) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned ticket = atomicInc(a.ctrl, gridDim.x - 1);
+            s.last = (ticket == gridDim.x - 1);
+        }
+        __syncthreads();
+        if (s.last) {
+            __threadfence();
+            float v = 0.f;
+            for (int row = tid; row < B; row += 256) v += __ldcg(a.rowloss + row);
+            s.red[tid] = v;
+            __syncthreads();
+            for (int o = 128; o > 0; o >>= 1) {
+                if (tid < o) s.red[tid] += s.red[tid + o];
+                __syncthreads();
+            }
+            if (tid == 0) {
+                const float mean = s.red[0] * invB;
+                a.loss[0] = mean;
+                a.loss[1] += mean * invB;
+            }
+        }
+    }
+}
+
+static int launch_rows_gemm(const RowsArgs& a, cudaStream_t st) {
+    static bool configured[64] = {};
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    const size_t smem = sizeof(RowsGemmSmem);
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        DDPM_CUDA(cudaFuncSetAttribute(rows_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev] = true;
+    }
+    int grid = (a.B + RG_ROWS - 1) / RG_ROWS;
+    if (grid > 148) grid = 148;
+    rows_gemm_kernel<<<grid, 256, smem, st>>>(a);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // GRADS: C[m][n] = scale * sum_b A[b][m] * Bm[b][n]   (reduction over the batch)
 // ------------------------------------------------------------------------------------------
 struct GradArgs {
@@ -577,8 +848,13 @@ __device__ void grad_tile(const GradArgs& a, const float* __restrict__ A, int ld
 #pragma unroll
             for (int k = 0; k < KCHUNK; ++k) {
                 float av[TM], bv[TN];
+                if (TM == 4) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(As + k * AS + ty * 4);
+                    av[0] = t4.x; av[1] = t4.y; av[TM - 2] = t4.z; av[TM - 1] = t4.w;
+                } else {
 #pragma unroll
-                for (int i = 0; i < TM; ++i) av[i] = As[k * AS + ty * TM + i];
+                    for (int i = 0; i < TM; ++i) av[i] = As[k * AS + ty * TM + i];
+                }
 #pragma unroll
                 for (int j4 = 0; j4 < TN / 4; ++j4) {
                     const float4 t4 = *reinterpret_cast<const float4*>(Bs + k * BS + tx * TN + j4 * 4);
@@ -631,6 +907,16 @@ grads_kernel(GradArgs a) {
         const int bs = work / GRAD_ITEMS, item = work - bs * GRAD_ITEMS;
         const int b0 = bs * slice, b1 = min(a.B, b0 + slice);
         if (item < N_GW1) {
+            if (a.bsplit > 1) {
+                // sliced (large) batches: 14 tiles of 64 x 112 with 4 x 8 register blocks (32 FMAs per 3 LDS.128);
+                // items 14..55 of this slice have nothing to do
+                if (item < (HID / 64) * (IN / 112)) {
+                    const int mt = item / (IN / 112), nt = item - mt * (IN / 112);
+                    grad_tile<64, 112, 4, 8, U8>(a, a.dz1, HID, mt * 64, HID, a.x, IN, nt * 112, DDPM_OFF_W1, IN, As, Bs, lut,
+                                                 b0, b1, bs);
+                }
+                continue;
+            }
             const int mt = item / (IN / GW1_BN), nt = item - mt * (IN / GW1_BN);
             grad_tile<GW1_BM, GW1_BN, 2, 4, U8>(a, a.dz1, HID, mt * GW1_BM, HID, a.x, IN, nt * GW1_BN,
                                                 DDPM_OFF_W1, IN, As, Bs, lut, b0, b1, bs);
@@ -755,6 +1041,7 @@ static int launch_rows(const RowsArgs& a, cudaStream_t st) {
 }
 
 static int launch_rows_any(const RowsArgs& a, cudaStream_t st) {
+    if (a.B >= 512 && !(a.flags & ROWS_BWD_ONLY)) return launch_rows_gemm(a, st);   // GEMM-style chain, 32 rows per pass
     if (a.B <= 148) return launch_rows<1>(a, st);
     if (a.B <= 592) return launch_rows<2>(a, st);
     return launch_rows<4>(a, st);
