@@ -113,11 +113,14 @@ int ddpm_step_forward(const float* d_params,
  * If d_dlogits != NULL it is used as dL/dlogits f32[batch,10] (autograd path: any upstream loss);
  * otherwise the forward must have been called with DDPM_FWD_PREP_BACKWARD.
  * If lr != 0 the SGD update p <- fma(-lr, g, p) (optimizer.step(), mp:463) is fused into the
- * gradient epilogue (single-GPU fast path; d_params is written). */
+ * gradient epilogue (single-GPU fast path; d_params is written).
+ * flags: DDPM_BWD_TF32 computes fc1's weight gradient dW1 = dz1^T . X with tcgen05 TF32 tensor-core MMAs
+ * (batch >= 2048 and the resident uint8 dataset path only; ignored otherwise); ~1e-3 relative. */
+#define DDPM_BWD_TF32 1u
 int ddpm_step_backward(float* d_params,
                        const uint8_t* d_images, int64_t n_samples,
                        const int64_t* d_idx, const float* d_x,
-                       const float* d_dlogits, int batch, float grad_scale, float lr,
+                       const float* d_dlogits, int batch, float grad_scale, float lr, unsigned flags,
                        float* d_grads, void* d_workspace, void* stream);
 
 /* Persistent step kernel (small-batch fast path): ONE cooperative launch runs `nsteps` complete

@@ -16,9 +16,10 @@ LIB_PATH = os.path.join(_HERE, "libddpmnist_b200.so")
 IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
 FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
+BWD_TF32 = 1
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class DDPMError(RuntimeError):
@@ -59,7 +60,7 @@ SIGNATURES = {
     "ddpm_comm_destroy": (None, [_vp]),
     "ddpm_train_steps_fused_ddp": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _u64, _u64, _i32, _i32, _u32,
                                           _f32, _vp, _vp, _vp, _vp]),
-    "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _vp, _vp, _vp]),
+    "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _u32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),
     "ddpm_cdf5_open": (_i32, [C.c_char_p, C.POINTER(_vp)]),

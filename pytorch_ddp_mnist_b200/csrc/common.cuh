@@ -96,6 +96,9 @@ WsLayout ws_layout(int max_batch);
 
 // fc1 forward on tcgen05 tensor cores (csrc/fc1_tc.cu)
 int fc1_tc_ksplit();
+int dw1_tc_slices(int batch);
+int launch_dw1_tc(const float* dz1, const uint8_t* images, int64_t n_samples, const int64_t* idx, int B, float* gpart,
+                  cudaStream_t st);
 int launch_fc1_tc(const float* W1, const uint8_t* images, int64_t n_samples, const int64_t* idx, int B, float* part,
                   cudaStream_t st);
 

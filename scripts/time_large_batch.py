@@ -12,7 +12,7 @@ for B in (1024, 4096):
     idx = torch.randperm(240000, device=dev).to(torch.int64)
     for tf32 in (False, True):
         def fwd(i): ops.step_forward(eng.params, eng.ws, B, images=images, labels=labels, idx=idx[(i % 50) * B:(i % 50 + 1) * B], philox=(1, i), prep_backward=True, loss=eng.loss, tf32=tf32)
-        def bwd(i): ops.step_backward(eng.params, eng.ws, B, images=images, idx=idx[(i % 50) * B:(i % 50 + 1) * B], lr=0.01)
+        def bwd(i): ops.step_backward(eng.params, eng.ws, B, images=images, idx=idx[(i % 50) * B:(i % 50 + 1) * B], lr=0.01, tf32=tf32)
         for i in range(5): fwd(i); bwd(i)
         torch.cuda.synchronize()
         e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]

@@ -411,7 +411,7 @@ def test_persistent_philox_matches_three_kernel_path(ops, dev, data, golden):
 TOL_TF32 = 1e-3      # BASELINE.json north_star: "<= 1e-3 relative for TF32 GEMMs"
 
 
-@pytest.mark.parametrize("batch", [64, 200, 1024, 4096])
+@pytest.mark.parametrize("batch", [64, 200, 1024, 2048, 4096])
 def test_tf32_tensor_core_fc1_matches_fp32_path(ops, dev, data, golden, batch):
     """DDPM_FWD_TF32 routes fc1 through tcgen05.mma (TF32 operands, FP32 accumulate in TMEM)."""
     g = golden["traj_ws1"]
@@ -435,7 +435,7 @@ def test_tf32_tensor_core_fc1_matches_fp32_path(ops, dev, data, golden, batch):
         grads = torch.zeros(O.N_PARAMS, device=dev)
         ops.step_forward(params, ws, batch, images=images, labels=labels, idx=idx, mask=mask, prep_backward=True,
                          logits=logits, loss=loss, tf32=tf32)
-        ops.step_backward(params, ws, batch, images=images, idx=idx, grads=grads)
+        ops.step_backward(params, ws, batch, images=images, idx=idx, grads=grads, tf32=tf32)   # batch >= 2048: dW1 on tcgen05 too
         torch.cuda.synchronize()
         out[tf32] = (logits.cpu().numpy(), float(loss[0]), grads.cpu().numpy())
     lg, ls, gd = out[True]
