@@ -140,7 +140,10 @@ def _config(args, extra=None):
          "steps_per_launch_or_graph": CHUNK,
          "step_kernel": "three-kernel (v1)" if args.three_kernel or args.batch > 512 else "persistent (v2)",
          "gradient_exchange": "NCCL allreduce between kernels" if args.no_fused else
-                              "in-kernel over NVLink peer memory (pull, fixed rank order), ws > 1 only"}
+                              "in-kernel over NVLink peer memory (flag-in-data pushes, sums in fixed rank order; fc1's "
+                              "gradient exchange replaced by the dz1 row exchange), ws > 1 only"}
+    if args.batch > 512:
+        c["tensor_cores"] = "fc1 forward + dW1 on tcgen05 TF32" if args.tf32 else "off (fp32 FFMA)"
     if extra:
         c.update(extra)
     return c
@@ -157,6 +160,7 @@ def main() -> None:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fused", action="store_true", help="ws > 1: NCCL allreduce between kernels instead of the fused peer-memory exchange")
     ap.add_argument("--three-kernel", action="store_true", help="use the v1 three-kernel step instead of the persistent kernel")
+    ap.add_argument("--tf32", action="store_true", help="batch > 512 only: fc1 forward and dW1 on tcgen05 TF32 tensor cores (fp32 accumulate)")
     ap.add_argument("--cpu-baseline-steps", type=int, default=150)
     args = ap.parse_args()
     if args.warmup < 3:
@@ -204,7 +208,7 @@ def main() -> None:
         assert torch.equal(shards_all_dev[rank], shard_dev)
 
     torch.manual_seed(0)
-    eng = E.TrainEngine(dev, B, lr=0.01, world_size=world, rank=rank)
+    eng = E.TrainEngine(dev, B, lr=0.01, world_size=world, rank=rank, tf32=args.tf32 and B > 512)
     eng.load_state_dict(E.init_params_like_reference())
     eng.broadcast_params()
 
@@ -287,7 +291,7 @@ def main() -> None:
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": _config(args, {"final_batch_loss": final_loss}),
+        "dtype": "tf32" if eng.tf32 else "f32", "data": "synthetic", "config": _config(args, {"final_batch_loss": final_loss}),
         "gpu_launches": launches, "clocks": clocks, "e2e": e2e, "roofline": kern["roofline"],
         "kernels": kern["kernels"],
     }
@@ -337,10 +341,11 @@ def _time_kernels(torch, ops, eng, resident, shard_dev, B, world, three_kernel=F
     # forward = fc1_fwd + rows; backward = grads (+sgd when ws>1).  Separate them by difference.
     def fwd(idx):
         ops.step_forward(params, eng.ws, B, images=resident.images, labels=resident.labels, idx=idx,
-                         prep_backward=True, loss=eng.loss, **mask_kw)
+                         prep_backward=True, loss=eng.loss, tf32=eng.tf32, **mask_kw)
 
     def bwd(idx):
-        ops.step_backward(params, eng.ws, B, images=resident.images, idx=idx, grads=grads, grad_scale=gscale, lr=lr)
+        ops.step_backward(params, eng.ws, B, images=resident.images, idx=idx, grads=grads, grad_scale=gscale, lr=lr,
+                          tf32=eng.tf32)
 
     def gather_only(idx):
         ops.gather_decode(resident.images, resident.labels, idx, out_x=xbuf, out_y=ybuf)

@@ -43,8 +43,9 @@ def init_params_like_reference(generator: Optional[torch.Generator] = None) -> D
 
 class TrainEngine:
     def __init__(self, device, max_batch: int, lr: float = 0.01, world_size: int = 1, rank: int = 0,
-                 group=None, seed: int = 42):
+                 group=None, seed: int = 42, tf32: bool = False):
         self.device = torch.device(device)
+        self.tf32 = bool(tf32)                    # fc1 forward / dW1 on tcgen05 TF32 (three-kernel step, batch >= 128 / 2048)
         self.max_batch = int(max_batch)
         self.lr = float(lr)
         self.world_size, self.rank, self.group = int(world_size), int(rank), group
@@ -106,13 +107,13 @@ class TrainEngine:
             kw = dict(mask=mask)
         self.step_count += 1
         ops.step_forward(self.params, self.ws, b, images=resident.images, labels=resident.labels, idx=idx,
-                         prep_backward=True, loss=self.loss, **kw)
+                         prep_backward=True, loss=self.loss, tf32=self.tf32, **kw)
         if self.world_size == 1:
-            ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, lr=self.lr)
+            ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, lr=self.lr, tf32=self.tf32)
         else:
             import torch.distributed as dist
             ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
-                              grad_scale=1.0 / self.world_size)
+                              grad_scale=1.0 / self.world_size, tf32=self.tf32)
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
             ops.sgd_step(self.params, self.grads, self.lr)
 
