@@ -185,6 +185,38 @@ int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,
                                int batch, int nsteps, unsigned flags, float lr,
                                float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);
 
+/* -------------------------------------------------------------------------------- host-fed training loop
+ * The reference's inner loop with a HOST-side loader (mp:452-466): every step the batch arrives in
+ * host memory, is copied to the device, trained on, and the loss is read back:
+ *     for x, y in train_loader:  x, y = x.to(device), y.to(device) ... batch_loss.item()
+ * Here the whole loop is one call.  A feed owns a ring of `slots` batch slots in device memory, a
+ * copy stream and a table of sequence numbers.  ddpm_train_steps_host_fed launches the persistent
+ * step kernel for up to slots/2 steps at a time and, while it runs, streams every step's u8 pixels
+ * and labels from the caller's PINNED host buffers into the ring (cudaMemcpyAsync on the copy
+ * stream) followed by an 8-byte sequence word; the kernel waits for the sequence word of a step
+ * before it reads that step's pixels (bounded ~3 s, then it sets the feed's error word and carries
+ * on: no GPU hang).  Ring halves are recycled with events (copy stream waits for the kernel that
+ * last read the half).  Each step's mean loss is stored by the kernel straight into the caller's
+ * pinned host array (h_loss_steps; mapped host memory, one 4-byte PCIe write per step), so the
+ * host->device copy of the inputs and the device->host delivery of the result happen every step
+ * without a launch or a synchronisation per step.
+ *   batch <= 512; slots: power of two, 4 <= slots <= 4096
+ *   h_pixels  u8[nsteps][batch][784], h_labels u8[nsteps][batch]: pinned (cudaHostAlloc /
+ *             cudaHostRegister) host memory; must stay valid until `stream` has passed this call
+ *   comm      NULL (single GPU) or a connected communicator: the gradient bucket is then averaged
+ *             inside the kernel exactly as in ddpm_train_steps_fused_ddp with d_idx_all == NULL
+ *   h_loss_steps f32[nsteps] pinned host memory or NULL; d_loss as in ddpm_step_forward
+ * Arithmetic and results are those of ddpm_train_steps_persistent on the same batches (bit-exact). */
+typedef struct ddpm_feed ddpm_feed;
+int  ddpm_feed_create(int batch, int slots, ddpm_feed** out);
+int  ddpm_feed_error(const ddpm_feed* f, int* h_err);
+void ddpm_feed_destroy(ddpm_feed* f);
+int  ddpm_train_steps_host_fed(ddpm_feed* feed, ddpm_comm* comm, float* d_params,
+                               const uint8_t* h_pixels, const uint8_t* h_labels,
+                               const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
+                               int nsteps, unsigned flags, float lr,
+                               float* d_loss, float* h_loss_steps, void* d_workspace, void* stream);
+
 /* Forward/eval step for callers that cannot allocate.  No counterpart in the reference (added for
  * embedding; the reference is a script that allocates freely through torch).
  *

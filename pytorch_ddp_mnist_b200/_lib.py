@@ -19,7 +19,7 @@ FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
 BWD_TF32 = 1
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class DDPMError(RuntimeError):
@@ -60,6 +60,10 @@ SIGNATURES = {
     "ddpm_comm_destroy": (None, [_vp]),
     "ddpm_train_steps_fused_ddp": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _u64, _u64, _i32, _i32, _u32,
                                           _f32, _vp, _vp, _vp, _vp]),
+    "ddpm_feed_create": (_i32, [_i32, _i32, C.POINTER(_vp)]),
+    "ddpm_feed_error": (_i32, [_vp, C.POINTER(_i32)]),
+    "ddpm_feed_destroy": (None, [_vp]),
+    "ddpm_train_steps_host_fed": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _u64, _i32, _u32, _f32, _vp, _vp, _vp, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _u32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),

@@ -40,7 +40,8 @@ constexpr int N_W2T = 32;                             // dW2 tiles: 8 row tiles 
 constexpr int N_W3T = 4;                              // dW3 column tiles (32 cols); the same CTAs do db1, db2, loss
 constexpr int CTA_W2 = N_W1, CTA_W3 = N_W1 + N_W2T;
 constexpr int P_GRID = CTA_W3 + N_W3T;                // 148 = one CTA per SM
-constexpr int N_SMALL = N_W2T + N_W3T;                // 36 CTAs update W2, W3, b1, b2
+constexpr int N_SMALL = N_W2T + N_W3T;                // 36 CTAs update W2, W3, b2
+constexpr int N_READY = N_SMALL + N_W1 / N_NT;        // ... plus the 8 W1 CTAs (pixel tile 0) that update b1: bumps of the 'ready' counter per step
 constexpr int CR = 64;                                // batch rows per smem chunk
 constexpr int XS_LD = 60;                             // padded row of the decoded pixel tile (16B aligned)
 constexpr int PERSIST_MAX_BATCH = 512;
@@ -71,6 +72,9 @@ struct PersistArgs {
     unsigned long long* xrecv_dz[DDPM_MAX_WORLD];     // every rank's buffer [2 parities][world sources][CR rows][ACT_ROW_WORDS]
     const int64_t* idx_all; size_t idx_stride;        // i64 [world][idx_stride]: every rank's batches of this launch
     int act_exchange;
+    // ---- host-fed mode: the batches of this launch arrive in a device ring while the kernel runs; step s may read
+    // its slot once feed_flags[(feed_g0 + s) % feed_slots] == feed_g0 + s + 1
+    const unsigned long long* feed_flags; unsigned long long feed_g0; int feed_slots; int* feed_err;
 };
 
 struct __align__(16) PersistSmem {
@@ -85,6 +89,7 @@ struct __align__(16) PersistSmem {
     float red[2 * HID];
     float zs[NCP], dzs[NCP];
     int ylab;
+    int feed_ok;                                      // host-fed mode: next step's slot was already full at the early probe
     float lut[256];
 };
 
@@ -126,6 +131,23 @@ __device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned l
     grid_wait(ctr, target);
 }
 
+// host-fed mode: slot of step `step` filled?  The copy stream carries pixels, labels and then a stream memory
+// operation that writes the sequence word behind a system-wide fence (cuStreamWriteValue64); the data loads that
+// follow go to L2 (.cg), never to a stale L1 line.
+__device__ __forceinline__ bool feed_ready(const PersistArgs& a, int step) {
+    const unsigned long long g = a.feed_g0 + (unsigned long long)step;
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(a.feed_flags + (g & (unsigned long long)(a.feed_slots - 1))) : "memory");
+    return v == g + 1;
+}
+__device__ __forceinline__ void feed_wait(const PersistArgs& a, int step) {
+    if (feed_ready(a, step)) return;
+    if (*(volatile int*)a.feed_err) return;                                // already timed out once: do not wait again
+    const long long t0 = clock64();
+    while (!feed_ready(a, step))
+        if (clock64() - t0 > 6000000000LL) { *a.feed_err = 1; break; }     // ~3 s: the host stopped feeding
+}
+
 __device__ __forceinline__ int w1_idx(int m, int n) { return (((n >> 2) * MT + m) << 2) + (n & 3); }   // [n/4][m][n%4]
 
 // Pixel tile [rows c0..c0+CR) x [56 pixels of tile nt]: loads first (all index loads, then all
@@ -143,6 +165,7 @@ __device__ __forceinline__ void tile_load_idx(PixelRegs& px, const PersistArgs& 
         px.sidx[i] = (t < CR * PX_PER_ROW && row < a.B) ? __ldg(idx + row) : -1;
     }
 }
+template <bool FEED>
 __device__ __forceinline__ void tile_load_px(PixelRegs& px, const PersistArgs& a, int nt) {
     px.ok = 0;
 #pragma unroll
@@ -151,12 +174,14 @@ __device__ __forceinline__ void tile_load_px(PixelRegs& px, const PersistArgs& a
         const int q = t % PX_PER_ROW;
         const bool ok = (px.sidx[i] >= 0 && px.sidx[i] < a.n_samples);
         px.ok |= (ok ? 1u : 0u) << i;
-        px.v[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(a.images + px.sidx[i] * IN + nt * NT) + q) : 0u;
+        if (FEED) px.v[i] = ok ? __ldcg(reinterpret_cast<const uint32_t*>(a.images + px.sidx[i] * IN + nt * NT) + q) : 0u;
+        else      px.v[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(a.images + px.sidx[i] * IN + nt * NT) + q) : 0u;
     }
 }
+template <bool FEED>
 __device__ __forceinline__ void tile_load(PixelRegs& px, const PersistArgs& a, const int64_t* idx, int c0, int nt) {
     tile_load_idx(px, a, idx, c0);
-    tile_load_px(px, a, nt);
+    tile_load_px<FEED>(px, a, nt);
 }
 
 __device__ __forceinline__ void tile_store(const PixelRegs& px, PersistSmem& s, float* xs) {
@@ -326,6 +351,7 @@ __device__ __forceinline__ void act_stage(const PersistArgs& a, unsigned long lo
     }
 }
 
+template <bool FEED>                                  // FEED: host-fed mode (batches arrive in a device ring while the kernel runs)
 __global__ void __launch_bounds__(P_THREADS, 1)
 train_persist_kernel(PersistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -352,7 +378,10 @@ train_persist_kernel(PersistArgs a) {
             const float4 v = *reinterpret_cast<const float4*>(a.params + DDPM_OFF_W1 + (size_t)(mt * MT + m) * IN + nt * NT + q * 4);
             *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, q * 4)]) = v;
         }
-        if (single) tile_load(px, a, a.idx, 0, nt);
+        if (single) {
+            if (FEED) feed_wait(a, 0);
+            tile_load<FEED>(px, a, a.idx, 0, nt);
+        }
     }
     __syncthreads();                                   // lut ready
     if (own_w1 && single) tile_store(px, s, s.xs[0]);
@@ -381,11 +410,15 @@ train_persist_kernel(PersistArgs a) {
             const int m = tid & 15, rg = tid >> 4;            // 16 row groups x 4 rows
             if (prefetch) tile_load_idx(px, a, idx + B, 0);   // next step's sample indices: in flight during phase A
             if (tid == BAR_TID && step > 0 && cta < B) ready_seen = ld_relaxed64(&a.bar[1]);
+            if (FEED && tid == 64) {
+                if (prefetch) s.feed_ok = feed_ready(a, step + 1) ? 1 : 0;   // early probe; re-checked before the pixel loads
+                if (!single) feed_wait(a, step);
+            }
             __syncthreads();                                  // last step's in-place W1 tile update is complete
             for (int c = 0; c < nchunks; ++c) {
                 if (!single) {
                     __syncthreads();
-                    tile_load(px, a, idx, c * CR, nt);
+                    tile_load<FEED>(px, a, idx, c * CR, nt);
                     tile_store(px, s, xs_cur);
                     __syncthreads();
                 }
@@ -408,7 +441,10 @@ train_persist_kernel(PersistArgs a) {
             }
             // next step's pixels do not depend on the weights: start fetching them now, decode
             // them after phase B; the two round trips hide behind the barrier waits
-            if (prefetch && tid != BAR_TID) tile_load_px(px, a, nt);
+            if (prefetch && tid != BAR_TID) {
+                if (FEED && !s.feed_ok) feed_wait(a, step + 1);
+                tile_load_px<FEED>(px, a, nt);
+            }
         }
         DBG_STAMP(1);
         grid_arrive(a.bar, bar_target);
@@ -424,7 +460,7 @@ train_persist_kernel(PersistArgs a) {
                 // (no fence: the owners released their updates before bumping the counter, and W2/W3/b are
                 //  read below with L2-coherent .cg loads that are issued only after this check succeeded)
                 if (tid == BAR_TID) {
-                    const unsigned long long need = ready_base + (unsigned long long)N_SMALL * step;
+                    const unsigned long long need = ready_base + (unsigned long long)N_READY * step;
                     while (ready_seen < need) ready_seen = ld_relaxed64(&a.bar[1]);
                 }
                 __syncthreads();
@@ -437,14 +473,19 @@ train_persist_kernel(PersistArgs a) {
             __pipeline_commit();
             if (tid == 32) {                                  // label of this CTA's first row: two dependent loads,
                 const int64_t sidx = __ldg(idx + cta);        // kept off the barrier thread and off warp 0
-                yv_first = (sidx >= 0 && sidx < a.n_samples) ? __ldg(a.labels + sidx) : 0;
+                if (FEED) feed_wait(a, step);
+                const bool ok = sidx >= 0 && sidx < a.n_samples;
+                yv_first = !ok ? 0 : (FEED ? __ldcg(a.labels + sidx) : __ldg(a.labels + sidx));
             }
         }
         grid_wait(a.bar, bar_target);
         // the barrier thread kept its own memory pipeline empty while it was fencing; it catches up now
         if (tid == BAR_TID) {
             if (cta < B) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
-            if (prefetch) tile_load_px(px, a, nt);
+            if (prefetch) {
+                if (FEED && !s.feed_ok) feed_wait(a, step + 1);
+                tile_load_px<FEED>(px, a, nt);
+            }
         }
         DBG_STAMP(2);
 
@@ -460,7 +501,8 @@ train_persist_kernel(PersistArgs a) {
                     int yv = yv_first;
                     if (row != cta) {
                         const int64_t sidx = __ldg(idx + row);
-                        yv = (sidx >= 0 && sidx < a.n_samples) ? __ldg(a.labels + sidx) : 0;
+                        const bool ok = sidx >= 0 && sidx < a.n_samples;
+                        yv = !ok ? 0 : (FEED ? __ldcg(a.labels + sidx) : __ldg(a.labels + sidx));
                     }
                     s.ylab = yv;                              // read by warp 0 after three more barriers
                 }
@@ -626,18 +668,18 @@ train_persist_kernel(PersistArgs a) {
             int nxt = -1;
             if (actx) {
                 nxt = (a.rank == 0) ? 1 : 0;
-                tile_load(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
+                tile_load<FEED>(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
             }
             for (int c = 0; c < npass; ++c) {
                 __syncthreads();
                 const float* xs_src = xs_cur;
                 if (!actx) {
-                    if (!single) { tile_load(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
+                    if (!single) { tile_load<FEED>(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
                 } else if (c != a.rank) {
                     tile_store(px, s, s.xsx);
                     xs_src = s.xsx;
                     nxt = c + 1 + ((c + 1 == a.rank) ? 1 : 0);
-                    if (nxt < a.world) tile_load(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
+                    if (nxt < a.world) tile_load<FEED>(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
                 }
                 if (!actx) {
                     const int r = tid >> 2, q = tid & 3, row = c * CR + r;      // 64 rows x 4 float4
@@ -679,6 +721,10 @@ train_persist_kernel(PersistArgs a) {
                 const float pold = __ldcg(a.params + offb);
                 if (ddp && !actx) ll_allreduce<1>(a, T, cta, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pold);
+                // b1 is read by every row CTA at the start of the next step: its 8 writers count towards 'ready' too
+                // (row CTAs that own no W1 tile - batch > 112 - get there long before this CTA leaves phase C)
+                __syncwarp(0x0000ffffu);
+                if (tid == 224 && a.lr != 0.f) red_release64(&a.bar[1]);
             }
             float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
             if (act) {
@@ -904,11 +950,15 @@ static int persist_configure() {
     DDPM_CUDA(cudaGetDevice(&dev));
     const int smem = (int)sizeof(PersistSmem);
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        DDPM_CUDA(cudaFuncSetAttribute(train_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        int per_sm = 0, sms = 0;
-        DDPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, train_persist_kernel, P_THREADS, smem));
+        int sms = 0;
         DDPM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        DDPM_CHECK_ARG(per_sm * sms >= P_GRID, "persistent kernel: device cannot co-schedule %d blocks", P_GRID);
+        const void* fns[2] = {(const void*)train_persist_kernel<false>, (const void*)train_persist_kernel<true>};
+        for (const void* fn : fns) {
+            int per_sm = 0;
+            DDPM_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            DDPM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, P_THREADS, smem));
+            DDPM_CHECK_ARG(per_sm * sms >= P_GRID, "persistent kernel: device cannot co-schedule %d blocks", P_GRID);
+        }
         configured[dev] = true;
     }
     return 0;
@@ -947,8 +997,8 @@ static int persist_fill_and_launch(PersistArgs& a, float* d_params, float* d_gra
     a.bar = (unsigned long long*)(ws + L.ctrl) + 2;     // ctrl words 4..7
     a.dbg = g_persist_dbg;
     void* kargs[] = {&a};
-    DDPM_CUDA(cudaLaunchCooperativeKernel((const void*)train_persist_kernel, dim3(P_GRID), dim3(P_THREADS), kargs,
-                                          sizeof(PersistSmem), (cudaStream_t)stream));
+    const void* fn = a.feed_flags ? (const void*)train_persist_kernel<true> : (const void*)train_persist_kernel<false>;
+    DDPM_CUDA(cudaLaunchCooperativeKernel(fn, dim3(P_GRID), dim3(P_THREADS), kargs, sizeof(PersistSmem), (cudaStream_t)stream));
     return 0;
 }
 
@@ -1042,6 +1092,16 @@ extern "C" void ddpm_comm_destroy(ddpm_comm* c) {
     delete c;
 }
 
+static void comm_fill(PersistArgs& a, const ddpm_comm* comm) {
+    a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
+    a.two_stage = comm->two_stage;
+    for (int r = 0; r < comm->world; ++r) {
+        a.xrecv[r] = (unsigned long long*)comm->peer[r];
+        a.xrecv_dz[r] = (unsigned long long*)((char*)comm->peer[r] + comm->recv_bytes);
+    }
+    a.xerr = (int*)((char*)comm->local + comm->recv_bytes + comm->dz_bytes);
+}
+
 extern "C" int ddpm_train_steps_fused_ddp(
         ddpm_comm* comm, float* d_params,
         const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
@@ -1057,13 +1117,7 @@ extern "C" int ddpm_train_steps_fused_ddp(
         DDPM_CHECK_ARG(comm->peer[r] != nullptr, "ddpm_train_steps_fused_ddp: rank %d is not connected (ddpm_comm_connect)", r);
     PersistArgs a;
     memset(&a, 0, sizeof(a));
-    a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
-    a.two_stage = comm->two_stage;
-    for (int r = 0; r < comm->world; ++r) {
-        a.xrecv[r] = (unsigned long long*)comm->peer[r];
-        a.xrecv_dz[r] = (unsigned long long*)((char*)comm->peer[r] + comm->recv_bytes);
-    }
-    a.xerr = (int*)((char*)comm->local + comm->recv_bytes + comm->dz_bytes);
+    comm_fill(a, comm);
     // fc1's gradient through the dz1 exchange when every rank's indices are known and the batch is one chunk
     a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
     if (a.act_exchange && getenv("DDPM_ACT_EXCHANGE_ALL") != nullptr) a.act_exchange = 2;   // also W2 / W3 / biases (measured slower at ws = 2)
@@ -1074,4 +1128,152 @@ extern "C" int ddpm_train_steps_fused_ddp(
                                            d_loss, d_loss_steps, d_workspace, stream, "ddpm_train_steps_fused_ddp");
     if (rc == 0) comm->steps += (unsigned long long)nsteps;
     return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// host-fed training loop: batches stream from pinned host memory into a device ring while the
+// persistent kernel consumes them (include/ddpmnist_b200.h, "host-fed training loop")
+// ------------------------------------------------------------------------------------------
+struct ddpm_feed {
+    int device = 0, batch = 0, slots = 0;
+    uint8_t* ring_x = nullptr;                   // [slots][batch][784]
+    uint8_t* ring_y = nullptr;                   // [slots][batch]
+    unsigned long long* flags = nullptr;         // [slots] sequence words, then one i32 error word
+    int64_t* ident = nullptr;                    // [slots*batch] = 0, 1, 2, ...: the ring viewed as a dataset
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t done[2] = {nullptr, nullptr};    // kernel that last read ring half h has finished
+    bool done_valid[2] = {false, false};
+    unsigned long long chunks = 0;               // chunk c uses ring half c & 1 and sequence numbers c * slots/2 + i
+};
+
+extern "C" void ddpm_feed_destroy(ddpm_feed* f) {
+    if (!f) return;
+    if (f->copy_stream) { cudaStreamSynchronize(f->copy_stream); cudaStreamDestroy(f->copy_stream); }
+    for (int h = 0; h < 2; ++h) if (f->done[h]) cudaEventDestroy(f->done[h]);
+    if (f->ring_x) cudaFree(f->ring_x);
+    if (f->ring_y) cudaFree(f->ring_y);
+    if (f->flags) cudaFree(f->flags);
+    if (f->ident) cudaFree(f->ident);
+    delete f;
+}
+
+// cuStreamWriteValue64 through the runtime's driver entry point lookup (no link-time dependency on libcuda)
+typedef int (*write_value64_fn)(cudaStream_t, unsigned long long, unsigned long long, unsigned);
+static write_value64_fn write_value64 = nullptr;
+static int resolve_write_value64() {
+    if (write_value64) return 0;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+    DDPM_CUDA(cudaGetDriverEntryPoint("cuStreamWriteValue64", &p, cudaEnableDefault, &q));
+    DDPM_CHECK_ARG(q == cudaDriverEntryPointSuccess && p != nullptr, "driver does not provide cuStreamWriteValue64 (status %d)", (int)q);
+    write_value64 = (write_value64_fn)p;
+    return 0;
+}
+
+extern "C" int ddpm_feed_create(int batch, int slots, ddpm_feed** out) {
+    DDPM_CHECK_ARG(out != nullptr, "ddpm_feed_create: null output");
+    *out = nullptr;
+    DDPM_CHECK_ARG(batch > 0 && batch <= PERSIST_MAX_BATCH, "ddpm_feed_create: batch %d outside [1, %d]", batch, PERSIST_MAX_BATCH);
+    DDPM_CHECK_ARG(slots >= 4 && slots <= 4096 && (slots & (slots - 1)) == 0,
+                   "ddpm_feed_create: slots must be a power of two in [4, 4096] (got %d)", slots);
+    if (resolve_write_value64()) return 1;
+    ddpm_feed* f = new ddpm_feed();
+    f->batch = batch; f->slots = slots;
+    const size_t nrow = (size_t)slots * batch;
+    cudaError_t e = cudaGetDevice(&f->device);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&f->ring_x, nrow * IN);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&f->ring_y, nrow);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&f->flags, (size_t)slots * 8 + 64);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&f->ident, nrow * sizeof(int64_t));
+    if (e == cudaSuccess) e = cudaMemset(f->flags, 0, (size_t)slots * 8 + 64);       // 0 never matches a sequence word (>= 1)
+    if (e == cudaSuccess) {
+        int64_t* h = (int64_t*)malloc(nrow * sizeof(int64_t));
+        if (!h) e = cudaErrorMemoryAllocation;
+        else {
+            for (size_t i = 0; i < nrow; ++i) h[i] = (int64_t)i;
+            e = cudaMemcpy(f->ident, h, nrow * sizeof(int64_t), cudaMemcpyHostToDevice);
+            free(h);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking);
+    for (int h = 0; h < 2 && e == cudaSuccess; ++h) e = cudaEventCreateWithFlags(&f->done[h], cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+        ddpm_feed_destroy(f);
+        return set_error("ddpm_feed_create: %s", cudaGetErrorString(e));
+    }
+    *out = f;
+    return 0;
+}
+
+extern "C" int ddpm_feed_error(const ddpm_feed* f, int* h_err) {
+    DDPM_CHECK_ARG(f && h_err, "ddpm_feed_error: null argument");
+    DDPM_CUDA(cudaMemcpy(h_err, f->flags + f->slots, sizeof(int), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int ddpm_train_steps_host_fed(
+        ddpm_feed* f, ddpm_comm* comm, float* d_params,
+        const uint8_t* h_pixels, const uint8_t* h_labels,
+        const uint8_t* d_masks, uint64_t philox_seed, uint64_t philox_step0,
+        int nsteps, unsigned flags, float lr,
+        float* d_loss, float* h_loss_steps, void* d_workspace, void* stream) {
+    const char* who = "ddpm_train_steps_host_fed";
+    DDPM_CHECK_ARG(f != nullptr && h_pixels != nullptr && h_labels != nullptr, "%s: null feed or host buffer", who);
+    DDPM_CHECK_ARG(nsteps > 0, "%s: nsteps must be positive (got %d)", who, nsteps);
+    DDPM_CHECK_ARG(lr != 0.f, "%s: lr must be non-zero", who);
+    int dev = -1;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    DDPM_CHECK_ARG(dev == f->device, "%s: feed was created on device %d, current device is %d", who, f->device, dev);
+    {   // both host buffers must be page-locked: a pageable source would make every cudaMemcpyAsync a staged, blocking copy
+        cudaPointerAttributes pa;
+        DDPM_CUDA(cudaPointerGetAttributes(&pa, h_pixels));
+        DDPM_CHECK_ARG(pa.type == cudaMemoryTypeHost, "%s: h_pixels is not pinned host memory", who);
+        DDPM_CUDA(cudaPointerGetAttributes(&pa, h_labels));
+        DDPM_CHECK_ARG(pa.type == cudaMemoryTypeHost, "%s: h_labels is not pinned host memory", who);
+    }
+    float* d_loss_steps = nullptr;
+    if (h_loss_steps) {
+        cudaError_t e = cudaHostGetDevicePointer((void**)&d_loss_steps, h_loss_steps, 0);
+        if (e != cudaSuccess) return set_error("%s: h_loss_steps is not mapped pinned host memory (%s)", who, cudaGetErrorString(e));
+    }
+    if (comm)
+        for (int r = 0; r < comm->world; ++r)
+            DDPM_CHECK_ARG(comm->peer[r] != nullptr, "%s: rank %d is not connected (ddpm_comm_connect)", who, r);
+    const int B = f->batch, H = f->slots / 2;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int done = 0; done < nsteps;) {
+        const int n = nsteps - done < H ? nsteps - done : H;
+        const int half = (int)(f->chunks & 1);
+        const unsigned long long g0 = f->chunks * (unsigned long long)H;
+        const size_t slot0 = (size_t)half * H;
+        // the copies of this chunk overwrite the half that the kernel of chunk c-2 read
+        if (f->done_valid[half]) DDPM_CUDA(cudaStreamWaitEvent(f->copy_stream, f->done[half], 0));
+        PersistArgs a;
+        memset(&a, 0, sizeof(a));
+        a.world = 1;
+        if (comm) comm_fill(a, comm);
+        a.feed_flags = f->flags; a.feed_g0 = g0; a.feed_slots = f->slots; a.feed_err = (int*)(f->flags + f->slots);
+        // the kernel goes first: it starts consuming while the copies below are still being enqueued
+        const int rc = persist_fill_and_launch(
+            a, d_params, nullptr, f->ring_x, f->ring_y, (int64_t)f->slots * B, f->ident + slot0 * B,
+            d_masks ? d_masks + (size_t)done * B * HID : nullptr, philox_seed, philox_step0 + (uint64_t)done, B, n, flags,
+            comm ? 1.0f / (float)comm->world : 1.0f, lr, d_loss, d_loss_steps ? d_loss_steps + done : nullptr,
+            d_workspace, stream, who);
+        if (rc) return rc;
+        if (comm) comm->steps += (unsigned long long)n;
+        DDPM_CUDA(cudaEventRecord(f->done[half], st));
+        f->done_valid[half] = true;
+        f->chunks += 1;
+        for (int i = 0; i < n; ++i) {
+            const size_t slot = slot0 + i, t = (size_t)done + i;
+            DDPM_CUDA(cudaMemcpyAsync(f->ring_x + slot * B * IN, h_pixels + t * B * IN, (size_t)B * IN, cudaMemcpyHostToDevice, f->copy_stream));
+            DDPM_CUDA(cudaMemcpyAsync(f->ring_y + slot * B, h_labels + t * B, (size_t)B, cudaMemcpyHostToDevice, f->copy_stream));
+            // sequence word: a stream memory operation, i.e. ordered after both copies AND preceded by a system-wide
+            // fence - two back-to-back DMA copies alone give a polling kernel no such guarantee
+            const int wr = write_value64(f->copy_stream, (unsigned long long)(uintptr_t)(f->flags + slot), g0 + i + 1, 0u);
+            DDPM_CHECK_ARG(wr == 0, "%s: cuStreamWriteValue64 failed (CUresult %d)", who, wr);
+        }
+        done += n;
+    }
+    return 0;
 }

@@ -56,6 +56,7 @@ class TrainEngine:
         self.ws = ops.Workspace(self.max_batch, self.device)
         self.step_count = 0                       # Philox stream position (perf-mode dropout)
         self.comm = None                          # fused data-parallel communicator (enable_fused_ddp)
+        self._feeds = {}                          # (batch, slots) -> ops.HostFeed (train_steps_host)
 
     # ------------------------------------------------------------------ parameters
     def views(self, flat: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
@@ -153,6 +154,32 @@ class TrainEngine:
                                        loss_steps=None if loss_steps is None else loss_steps[t:t + 1], **mk, **kw)
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
             ops.sgd_step(self.params, self.grads, self.lr)
+
+    def train_steps_host(self, host_pixels: torch.Tensor, host_labels: torch.Tensor, batch: int, nsteps: int,
+                         masks: Optional[torch.Tensor] = None, philox_step0: Optional[int] = None,
+                         host_loss_steps: Optional[torch.Tensor] = None, slots: int = 256) -> None:
+        """The reference's inner loop with a host-side loader (mp:452-466) as one call: `nsteps` batches in
+        PINNED host memory (u8 [nsteps, batch, 784] + u8 [nsteps, batch]) are streamed into a device ring
+        while the persistent kernel trains on them; every step's loss lands in `host_loss_steps` (pinned
+        f32[nsteps]).  ws > 1: needs `enable_fused_ddp()` (gradient average inside the kernel)."""
+        from ._lib import PERSIST_MAX_BATCH
+        if batch > PERSIST_MAX_BATCH:
+            raise ValueError(f"train_steps_host: batch {batch} > {PERSIST_MAX_BATCH}; use train_step_host_batch per step")
+        if self.world_size > 1 and self.comm is None:
+            raise RuntimeError("train_steps_host at world_size > 1 needs enable_fused_ddp()")
+        feed = self._feeds.get((batch, slots))
+        if feed is None:
+            feed = self._feeds[(batch, slots)] = ops.HostFeed(batch, slots)
+        st0 = self.step_count if philox_step0 is None else philox_step0
+        self.step_count += nsteps
+        mk = dict(masks=masks) if masks is not None else dict(philox=(self.seed, st0))
+        ops.train_steps_host_fed(feed, self.params, self.ws, nsteps, host_pixels=host_pixels, host_labels=host_labels,
+                                 comm=self.comm, lr=self.lr, loss=self.loss, host_loss_steps=host_loss_steps, **mk)
+
+    def check_feed(self) -> None:
+        for feed in self._feeds.values():
+            if feed.error():
+                raise RuntimeError("host-fed training loop: the kernel waited ~3 s for a batch that never arrived")
 
     def train_step_host_batch(self, x_u8: torch.Tensor, y_u8: torch.Tensor, idx_identity: torch.Tensor,
                               mask: Optional[torch.Tensor] = None) -> None:

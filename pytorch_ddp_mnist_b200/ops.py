@@ -239,6 +239,78 @@ def train_steps_fused_ddp(comm: FusedComm, params: torch.Tensor, ws: Workspace, 
                                          ptr(loss_steps), ptr(ws.buf), cur_stream()))
 
 
+class HostFeed:
+    """Ring of batch slots in device memory fed from pinned host memory while the persistent kernel
+    runs (ddpm_feed_*): the reference's `for x, y in train_loader: x.to(device) ... loss.item()` loop
+    (mp:452-466) as one call."""
+
+    def __init__(self, batch: int, slots: int = 256):
+        import ctypes as C
+        self.batch, self.slots = int(batch), int(slots)
+        self._h = C.c_void_p()
+        check(lib.ddpm_feed_create(self.batch, self.slots, C.byref(self._h)))
+
+    def error(self) -> int:
+        import ctypes as C
+        e = C.c_int(0)
+        check(lib.ddpm_feed_error(self._h, C.byref(e)))
+        return e.value
+
+    def close(self) -> None:
+        if self._h:
+            lib.ddpm_feed_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _need_pinned(t: Optional[torch.Tensor], name: str, dtype, optional=False):
+    if t is None:
+        if optional:
+            return
+        raise ValueError(f"{name} is required")
+    if t.is_cuda or not t.is_pinned():
+        raise ValueError(f"{name} must be a pinned host tensor")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+
+
+def train_steps_host_fed(feed: HostFeed, params: torch.Tensor, ws: Workspace, nsteps: int, *,
+                         host_pixels: torch.Tensor, host_labels: torch.Tensor,
+                         comm: Optional[FusedComm] = None,
+                         masks: Optional[torch.Tensor] = None, philox: Optional[Tuple[int, int]] = None,
+                         lr: float, loss: Optional[torch.Tensor] = None,
+                         host_loss_steps: Optional[torch.Tensor] = None) -> None:
+    """`nsteps` optimisation steps on batches that live in PINNED HOST memory (`host_pixels`
+    u8[nsteps, batch, 784], `host_labels` u8[nsteps, batch]): every step's batch is copied to the
+    device while the kernel runs and every step's loss is written to `host_loss_steps` (pinned
+    f32[nsteps]).  The host buffers must stay alive until the current stream has passed this call."""
+    _need(params, "params", torch.float32, (N_PARAMS,))
+    b = feed.batch
+    if b > ws.max_batch:
+        raise ValueError(f"batch {b} exceeds workspace max_batch {ws.max_batch}")
+    _need_pinned(host_pixels, "host_pixels", torch.uint8)
+    _need_pinned(host_labels, "host_labels", torch.uint8)
+    if host_pixels.numel() < nsteps * b * IN or host_labels.numel() < nsteps * b:
+        raise ValueError("host buffers shorter than nsteps*batch samples")
+    _need(masks, "masks", torch.uint8, (nsteps, b, HID), optional=True)
+    _need(loss, "loss", torch.float32, (2,), optional=True)
+    _need_pinned(host_loss_steps, "host_loss_steps", torch.float32, optional=True)
+    if host_loss_steps is not None and host_loss_steps.numel() < nsteps:
+        raise ValueError("host_loss_steps shorter than nsteps")
+    seed, step0 = philox if philox else (0, 0)
+    flags = _lib.FWD_PHILOX_MASK if philox else 0
+    check(lib.ddpm_train_steps_host_fed(feed._h, comm._h if comm is not None else None, ptr(params),
+                                        ptr(host_pixels), ptr(host_labels), ptr(masks), seed, step0, nsteps, flags, lr,
+                                        ptr(loss), ptr(host_loss_steps), ptr(ws.buf), cur_stream()))
+
+
 def cross_entropy(logits: torch.Tensor, y: torch.Tensor, loss: Optional[torch.Tensor] = None,
                   dlogits: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     _need(logits, "logits", torch.float32)

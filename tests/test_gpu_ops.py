@@ -387,6 +387,33 @@ def test_persistent_matches_oracle_all_batch_sizes(ops, dev, data, golden, batch
     assert np.abs(params.cpu().numpy() - want).max() < 1e-6
 
 
+@pytest.mark.parametrize("batch", [100, 128, 200, 512])
+def test_persistent_multi_step_launch_equals_single_step_launches(ops, dev, data, golden, batch):
+    """Batches above 112 make the small-gradient CTAs row CTAs as well: they reach the next step long before the
+    W1 CTAs have left phase C, so every parameter they read (b1 in particular) must be gated.  One 12-step launch,
+    twice, and 12 one-step launches must agree bit for bit."""
+    g = golden["traj_ws1"]
+    images, labels, _, _ = data
+    n = 12
+    rng = np.random.default_rng(31 + batch)
+    idx = torch.from_numpy(rng.integers(0, 60000, n * batch).astype(np.int64)).to(dev)
+    masks = torch.from_numpy((rng.random((n, batch, 128)) < 0.8).astype(np.uint8)).to(dev)
+    ws = ops.Workspace(batch, dev)
+    outs = []
+    for nper in (n, n, 1):
+        params = _flat(_params(g, "params0"), dev)
+        ls = torch.zeros(n, device=dev)
+        for s0 in range(0, n, nper):
+            ops.train_steps_persistent(params, ws, batch, nper, images=images, labels=labels,
+                                       idx=idx[s0 * batch:(s0 + nper) * batch], masks=masks[s0:s0 + nper].contiguous(),
+                                       lr=0.01, loss_steps=ls[s0:s0 + nper])
+        torch.cuda.synchronize()
+        outs.append((params.clone(), ls.clone()))
+    for o in outs[1:]:
+        assert torch.equal(outs[0][1], o[1])
+        assert torch.equal(outs[0][0], o[0])
+
+
 def test_persistent_philox_matches_three_kernel_path(ops, dev, data, golden):
     g = golden["traj_ws1"]
     images, labels, _, _ = data
@@ -449,3 +476,74 @@ def test_tf32_tensor_core_fc1_matches_fp32_path(ops, dev, data, golden, batch):
         assert _fro(gu[k], gr[k]) < 2e-2 and _rel(gu[k], gr[k]) < 5e-2, k
     # it really is a different arithmetic path (not a silent fall-back to the FFMA kernel)
     assert not np.array_equal(lg, out[False][0])
+
+
+# ------------------------------------------------------------------------------------------
+# host-fed loop: batches stream from pinned host memory into a device ring while the kernel runs
+# ------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,nsteps,slots", [(64, 100, 16), (64, 37, 256), (7, 50, 4), (200, 21, 8)])
+def test_host_fed_loop_bit_exact_with_resident_loop(ops, dev, data, golden, batch, nsteps, slots):
+    """Same batches, once gathered from the resident dataset by the persistent kernel and once streamed from
+    pinned host memory through a ring much shorter than the run (slot reuse, ring wrap, partial last chunk):
+    parameters, per-step losses (delivered in HOST memory) and the loss accumulator must be bit-identical.
+    At batch 64 the first run is the reference's own trajectory (golden)."""
+    g = golden["traj_ws1"]
+    images, labels, im, lb = data
+    rng = np.random.default_rng(77 + batch)
+    if batch == 64 and nsteps == 100:
+        idx_np = g["idx"].reshape(-1).astype(np.int64)
+        mask_np = O.unpack_masks(g["masks"])
+    else:
+        idx_np = rng.integers(0, 60000, nsteps * batch).astype(np.int64)
+        mask_np = (rng.random((nsteps, batch, 128)) < 0.8).astype(np.uint8)
+    masks = torch.from_numpy(mask_np).to(dev)
+    ws = ops.Workspace(batch, dev)
+    # resident
+    pa = _flat(_params(g, "params0"), dev)
+    la = torch.zeros(2, device=dev)
+    lsa = torch.zeros(nsteps, device=dev)
+    ops.train_steps_persistent(pa, ws, batch, nsteps, images=images, labels=labels, idx=torch.from_numpy(idx_np).to(dev),
+                               masks=masks, lr=0.01, loss=la, loss_steps=lsa)
+    torch.cuda.synchronize()
+    # host-fed, two calls (the second starts mid-ring)
+    hx = torch.from_numpy(im.reshape(-1, 784)[idx_np]).reshape(nsteps, batch, 784).contiguous().pin_memory()
+    hy = torch.from_numpy(lb[idx_np]).reshape(nsteps, batch).contiguous().pin_memory()
+    hl = torch.full((nsteps,), -1.0).pin_memory()
+    pb = _flat(_params(g, "params0"), dev)
+    lb2 = torch.zeros(2, device=dev)
+    feed = ops.HostFeed(batch, slots)
+    n1 = nsteps // 3
+    ops.train_steps_host_fed(feed, pb, ws, n1, host_pixels=hx[:n1], host_labels=hy[:n1], masks=masks[:n1].contiguous(),
+                             lr=0.01, loss=lb2, host_loss_steps=hl[:n1])
+    ops.train_steps_host_fed(feed, pb, ws, nsteps - n1, host_pixels=hx[n1:], host_labels=hy[n1:],
+                             masks=masks[n1:].contiguous(), lr=0.01, loss=lb2, host_loss_steps=hl[n1:])
+    torch.cuda.synchronize()
+    assert feed.error() == 0
+    assert torch.equal(pa, pb)
+    assert torch.equal(lsa.cpu(), hl)
+    assert torch.equal(la, lb2)
+    if batch == 64 and nsteps == 100:
+        assert np.abs(hl.numpy()[:5] - g["losses"][:5]).max() < 1e-5
+    feed.close()
+
+
+@pytest.mark.gpu
+def test_host_fed_argument_errors(ops, dev):
+    from pytorch_ddp_mnist_b200._lib import DDPMError
+    with pytest.raises(DDPMError, match="power of two"):
+        ops.HostFeed(64, 100)
+    with pytest.raises(DDPMError, match="batch"):
+        ops.HostFeed(1024, 16)
+    feed = ops.HostFeed(8, 4)
+    ws = ops.Workspace(8, dev)
+    params = torch.zeros(O.N_PARAMS, device=dev)
+    hx = torch.zeros(2, 8, 784, dtype=torch.uint8)
+    hy = torch.zeros(2, 8, dtype=torch.uint8)
+    with pytest.raises(ValueError, match="pinned"):
+        ops.train_steps_host_fed(feed, params, ws, 2, host_pixels=hx, host_labels=hy, lr=0.01)
+    with pytest.raises(ValueError, match="shorter"):
+        ops.train_steps_host_fed(feed, params, ws, 3, host_pixels=hx.pin_memory(), host_labels=hy.pin_memory(), lr=0.01)
+    with pytest.raises(DDPMError, match="lr"):
+        ops.train_steps_host_fed(feed, params, ws, 2, host_pixels=hx.pin_memory(), host_labels=hy.pin_memory(), lr=0.0)
+    feed.close()
