@@ -152,8 +152,8 @@ int ddpm_train_steps_persistent(float* d_params, float* d_grads,
  * (bit-identical replicas) and applies the SGD update in place.  No fences, no collective library
  * call and no kernel launch between steps.
  *
- * A communicator owns one symmetric device buffer (1.9 MB per rank of the job, the only device memory this library
- * allocates) that every peer process maps with CUDA IPC.  One process per GPU, all GPUs in one
+ * A communicator owns one symmetric device buffer (1.9 MB per rank of the job; besides a host feed's ring, below,
+ * the only device memory this library allocates) that every peer process maps with CUDA IPC.  One process per GPU, all GPUs in one
  * NVLink/P2P domain, world <= 8.  Set-up (host side, blocking):
  *   ddpm_comm_create(rank, world, &c)            on every rank (its GPU current)
  *   ddpm_comm_ipc_handle(c, handle64)            64-byte handle of the local buffer
@@ -190,13 +190,15 @@ int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,
  * host memory, is copied to the device, trained on, and the loss is read back:
  *     for x, y in train_loader:  x, y = x.to(device), y.to(device) ... batch_loss.item()
  * Here the whole loop is one call.  A feed owns a ring of `slots` batch slots in device memory, a
- * copy stream and a table of sequence numbers.  ddpm_train_steps_host_fed launches the persistent
+ * few copy streams and a sequence word per slot.  ddpm_train_steps_host_fed launches the persistent
  * step kernel for up to slots/2 steps at a time and, while it runs, streams every step's u8 pixels
- * and labels from the caller's PINNED host buffers into the ring (cudaMemcpyAsync on the copy
- * stream) followed by an 8-byte sequence word; the kernel waits for the sequence word of a step
- * before it reads that step's pixels (bounded ~3 s, then it sets the feed's error word and carries
- * on: no GPU hang).  Ring halves are recycled with events (copy stream waits for the kernel that
- * last read the half).  Each step's mean loss is stored by the kernel straight into the caller's
+ * and labels from the caller's PINNED host buffers into the ring (two cudaMemcpyAsync per step;
+ * step t on copy stream t % 4, since one stream's per-operation latency would cap the rate)
+ * followed by the slot's 8-byte sequence word (cuStreamWriteValue64: ordered after the copies and
+ * preceded by a system-wide fence); the kernel waits for the sequence word of a step before it
+ * reads that step's pixels (bounded ~3 s, then it sets the feed's error word and carries on: no
+ * GPU hang).  Ring halves are recycled with events (the copy streams wait for the kernel that last
+ * read the half).  Each step's mean loss is stored by the kernel straight into the caller's
  * pinned host array (h_loss_steps; mapped host memory, one 4-byte PCIe write per step), so the
  * host->device copy of the inputs and the device->host delivery of the result happen every step
  * without a launch or a synchronisation per step.

@@ -89,7 +89,6 @@ struct __align__(16) PersistSmem {
     float red[2 * HID];
     float zs[NCP], dzs[NCP];
     int ylab;
-    int feed_ok;                                      // host-fed mode: next step's slot was already full at the early probe
     float lut[256];
 };
 
@@ -134,11 +133,14 @@ __device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned l
 // host-fed mode: slot of step `step` filled?  The copy stream carries pixels, labels and then a stream memory
 // operation that writes the sequence word behind a system-wide fence (cuStreamWriteValue64); the data loads that
 // follow go to L2 (.cg), never to a stale L1 line.
-__device__ __forceinline__ bool feed_ready(const PersistArgs& a, int step) {
+__device__ __forceinline__ unsigned long long feed_word(const PersistArgs& a, int step) {
     const unsigned long long g = a.feed_g0 + (unsigned long long)step;
     unsigned long long v;
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(a.feed_flags + (g & (unsigned long long)(a.feed_slots - 1))) : "memory");
-    return v == g + 1;
+    return v;
+}
+__device__ __forceinline__ bool feed_ready(const PersistArgs& a, int step) {
+    return feed_word(a, step) == a.feed_g0 + (unsigned long long)step + 1;
 }
 __device__ __forceinline__ void feed_wait(const PersistArgs& a, int step) {
     if (feed_ready(a, step)) return;
@@ -404,16 +406,19 @@ train_persist_kernel(PersistArgs a) {
         const bool actx = ddp && a.act_exchange && single;           // W1 through the dz1 exchange
         const bool actx_all = actx && a.act_exchange == 2;           // ... and W2 / W3 / biases through dz2, h1d, h2, dz3
         const unsigned long long T = a.comm_step + step + 1;            // global step number of this communicator
+        float host_loss = 0.f;
+        unsigned long long feed_probe = 0;
 
         // ================================ phase A ================================
         if (own_w1) {
             const int m = tid & 15, rg = tid >> 4;            // 16 row groups x 4 rows
             if (prefetch) tile_load_idx(px, a, idx + B, 0);   // next step's sample indices: in flight during phase A
             if (tid == BAR_TID && step > 0 && cta < B) ready_seen = ld_relaxed64(&a.bar[1]);
-            if (FEED && tid == 64) {
-                if (prefetch) s.feed_ok = feed_ready(a, step + 1) ? 1 : 0;   // early probe; re-checked before the pixel loads
-                if (!single) feed_wait(a, step);
-            }
+            // early probe of the next step's sequence word by every thread: the load is in flight during phase A and
+            // is looked at only before the pixel loads (a probe through shared memory would put an L2 round trip in
+            // front of the bar.sync below: + 0.7 us per step, measured)
+            if (FEED && prefetch) feed_probe = feed_word(a, step + 1);
+            if (FEED && !single && tid == 64) feed_wait(a, step);
             __syncthreads();                                  // last step's in-place W1 tile update is complete
             for (int c = 0; c < nchunks; ++c) {
                 if (!single) {
@@ -442,7 +447,7 @@ train_persist_kernel(PersistArgs a) {
             // next step's pixels do not depend on the weights: start fetching them now, decode
             // them after phase B; the two round trips hide behind the barrier waits
             if (prefetch && tid != BAR_TID) {
-                if (FEED && !s.feed_ok) feed_wait(a, step + 1);
+                if (FEED && feed_probe != a.feed_g0 + (unsigned long long)step + 2) feed_wait(a, step + 1);
                 tile_load_px<FEED>(px, a, nt);
             }
         }
@@ -483,7 +488,7 @@ train_persist_kernel(PersistArgs a) {
         if (tid == BAR_TID) {
             if (cta < B) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
             if (prefetch) {
-                if (FEED && !s.feed_ok) feed_wait(a, step + 1);
+                if (FEED && feed_probe != a.feed_g0 + (unsigned long long)step + 2) feed_wait(a, step + 1);
                 tile_load_px<FEED>(px, a, nt);
             }
         }
@@ -908,7 +913,10 @@ train_persist_kernel(PersistArgs a) {
                 for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
                 if (lane == 0) {
                     const float mean = v * invB;
-                    if (a.loss_steps) a.loss_steps[step] = mean;
+                    // host-fed mode: loss_steps is HOST memory; a store over PCIe issued here would sit in front of this
+                    // thread's release of the 'ready' counter below (+ ~1 us on the next step's critical path)
+                    if (FEED) host_loss = mean;
+                    else if (a.loss_steps) a.loss_steps[step] = mean;
                     if (a.loss2) { a.loss2[0] = mean; a.loss2[1] += mean * invB; }
                 }
             }
@@ -917,6 +925,7 @@ train_persist_kernel(PersistArgs a) {
             __syncthreads();
             if (tid == 0) red_release64(&a.bar[1]);
         }
+        if (FEED && a.loss_steps && tid == 0 && cta == CTA_W3 + 2) a.loss_steps[step] = host_loss;
         DBG_STAMP(5);
         // no barrier here: W1 tiles are private; everything else is ordered by the next step's
         // first barrier (phase B of step t+1 starts only after every CTA finished phase C of t)
@@ -1140,7 +1149,12 @@ struct ddpm_feed {
     uint8_t* ring_y = nullptr;                   // [slots][batch]
     unsigned long long* flags = nullptr;         // [slots] sequence words, then one i32 error word
     int64_t* ident = nullptr;                    // [slots*batch] = 0, 1, 2, ...: the ring viewed as a dataset
-    cudaStream_t copy_stream = nullptr;
+    // step t is fed on copy stream t % nstreams: the three stream-ordered operations of a step (pixels, labels,
+    // sequence word) cost ~4.8 us of copy-queue latency on one stream (measured: 14.3 us/step at batch 64 against
+    // 8.5 us for the kernel); slots are independent, so consecutive steps overlap on different streams
+    static constexpr int MAX_STREAMS = 8;
+    int nstreams = 4;
+    cudaStream_t copy_stream[MAX_STREAMS] = {};
     cudaEvent_t done[2] = {nullptr, nullptr};    // kernel that last read ring half h has finished
     bool done_valid[2] = {false, false};
     unsigned long long chunks = 0;               // chunk c uses ring half c & 1 and sequence numbers c * slots/2 + i
@@ -1148,7 +1162,8 @@ struct ddpm_feed {
 
 extern "C" void ddpm_feed_destroy(ddpm_feed* f) {
     if (!f) return;
-    if (f->copy_stream) { cudaStreamSynchronize(f->copy_stream); cudaStreamDestroy(f->copy_stream); }
+    for (int i = 0; i < ddpm_feed::MAX_STREAMS; ++i)
+        if (f->copy_stream[i]) { cudaStreamSynchronize(f->copy_stream[i]); cudaStreamDestroy(f->copy_stream[i]); }
     for (int h = 0; h < 2; ++h) if (f->done[h]) cudaEventDestroy(f->done[h]);
     if (f->ring_x) cudaFree(f->ring_x);
     if (f->ring_y) cudaFree(f->ring_y);
@@ -1195,7 +1210,11 @@ extern "C" int ddpm_feed_create(int batch, int slots, ddpm_feed** out) {
             free(h);
         }
     }
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->copy_stream, cudaStreamNonBlocking);
+    if (const char* env = getenv("DDPM_FEED_STREAMS")) {
+        const int k = atoi(env);
+        if (k >= 1 && k <= ddpm_feed::MAX_STREAMS) f->nstreams = k;
+    }
+    for (int i = 0; i < f->nstreams && e == cudaSuccess; ++i) e = cudaStreamCreateWithFlags(&f->copy_stream[i], cudaStreamNonBlocking);
     for (int h = 0; h < 2 && e == cudaSuccess; ++h) e = cudaEventCreateWithFlags(&f->done[h], cudaEventDisableTiming);
     if (e != cudaSuccess) {
         ddpm_feed_destroy(f);
@@ -1247,7 +1266,8 @@ extern "C" int ddpm_train_steps_host_fed(
         const unsigned long long g0 = f->chunks * (unsigned long long)H;
         const size_t slot0 = (size_t)half * H;
         // the copies of this chunk overwrite the half that the kernel of chunk c-2 read
-        if (f->done_valid[half]) DDPM_CUDA(cudaStreamWaitEvent(f->copy_stream, f->done[half], 0));
+        if (f->done_valid[half])
+            for (int k = 0; k < f->nstreams; ++k) DDPM_CUDA(cudaStreamWaitEvent(f->copy_stream[k], f->done[half], 0));
         PersistArgs a;
         memset(&a, 0, sizeof(a));
         a.world = 1;
@@ -1266,11 +1286,12 @@ extern "C" int ddpm_train_steps_host_fed(
         f->chunks += 1;
         for (int i = 0; i < n; ++i) {
             const size_t slot = slot0 + i, t = (size_t)done + i;
-            DDPM_CUDA(cudaMemcpyAsync(f->ring_x + slot * B * IN, h_pixels + t * B * IN, (size_t)B * IN, cudaMemcpyHostToDevice, f->copy_stream));
-            DDPM_CUDA(cudaMemcpyAsync(f->ring_y + slot * B, h_labels + t * B, (size_t)B, cudaMemcpyHostToDevice, f->copy_stream));
+            cudaStream_t cs = f->copy_stream[i % f->nstreams];
+            DDPM_CUDA(cudaMemcpyAsync(f->ring_x + slot * B * IN, h_pixels + t * B * IN, (size_t)B * IN, cudaMemcpyHostToDevice, cs));
+            DDPM_CUDA(cudaMemcpyAsync(f->ring_y + slot * B, h_labels + t * B, (size_t)B, cudaMemcpyHostToDevice, cs));
             // sequence word: a stream memory operation, i.e. ordered after both copies AND preceded by a system-wide
             // fence - two back-to-back DMA copies alone give a polling kernel no such guarantee
-            const int wr = write_value64(f->copy_stream, (unsigned long long)(uintptr_t)(f->flags + slot), g0 + i + 1, 0u);
+            const int wr = write_value64(cs, (unsigned long long)(uintptr_t)(f->flags + slot), g0 + i + 1, 0u);
             DDPM_CHECK_ARG(wr == 0, "%s: cuStreamWriteValue64 failed (CUresult %d)", who, wr);
         }
         done += n;

@@ -157,7 +157,7 @@ class TrainEngine:
 
     def train_steps_host(self, host_pixels: torch.Tensor, host_labels: torch.Tensor, batch: int, nsteps: int,
                          masks: Optional[torch.Tensor] = None, philox_step0: Optional[int] = None,
-                         host_loss_steps: Optional[torch.Tensor] = None, slots: int = 256) -> None:
+                         host_loss_steps: Optional[torch.Tensor] = None, slots: Optional[int] = None) -> None:
         """The reference's inner loop with a host-side loader (mp:452-466) as one call: `nsteps` batches in
         PINNED host memory (u8 [nsteps, batch, 784] + u8 [nsteps, batch]) are streamed into a device ring
         while the persistent kernel trains on them; every step's loss lands in `host_loss_steps` (pinned
@@ -167,6 +167,10 @@ class TrainEngine:
             raise ValueError(f"train_steps_host: batch {batch} > {PERSIST_MAX_BATCH}; use train_step_host_batch per step")
         if self.world_size > 1 and self.comm is None:
             raise RuntimeError("train_steps_host at world_size > 1 needs enable_fused_ddp()")
+        if slots is None:                         # largest power of two whose ring stays under 64 MB (1024 at batch 64):
+            slots = 16                            # each launch covers slots/2 steps, a launch boundary costs ~30 us
+            while slots < 4096 and 2 * slots * batch * 785 <= (64 << 20):
+                slots *= 2
         feed = self._feeds.get((batch, slots))
         if feed is None:
             feed = self._feeds[(batch, slots)] = ops.HostFeed(batch, slots)
