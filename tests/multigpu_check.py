@@ -90,6 +90,7 @@ def main():
     other = mine.clone()
     dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "fused replicas diverged"
+    p20 = eng2.params.clone()
     # a second launch continues the flag sequence (communicator step counter) and stays in lock-step
     eng2.train_steps(res, idx[:4].reshape(-1).contiguous(), 64, 4, idx_all=idx_all[:, :4 * 64].contiguous())
     torch.cuda.synchronize()
@@ -98,6 +99,32 @@ def main():
     other = mine.clone()
     dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "fused replicas diverged after the second launch"
+    dist.barrier()
+
+    # ---- host-fed fused loop: this rank's batches stream from pinned host memory (ring of 8 slots: reuse + wrap),
+    # gradients averaged inside the kernel (full bucket exchange: other ranks' pixels are not on this device)
+    eng3 = E.TrainEngine(dev, 64, world_size=world, rank=rank)
+    eng3.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
+    eng3.enable_fused_ddp()
+    flat = idx.reshape(-1).cpu().numpy()
+    n = idx.shape[0]
+    hx = torch.from_numpy(im.reshape(-1, 784)[flat]).reshape(n, 64, 784).contiguous().pin_memory()
+    hy = torch.from_numpy(lb[flat]).reshape(n, 64).contiguous().pin_memory()
+    hl = torch.full((n,), -1.0).pin_memory()
+    eng3.train_steps_host(hx, hy, 64, n, masks=masks.contiguous(), host_loss_steps=hl, slots=8)
+    torch.cuda.synchronize()
+    eng3.check_comm()
+    eng3.check_feed()
+    if os.environ.get("DDPM_NO_ACT_EXCHANGE"):                 # same exchange as eng2 then: bit-identical
+        assert torch.equal(eng3.params, p20), "host-fed fused loop differs from the resident fused loop"
+        assert np.array_equal(hl.numpy(), l2)
+    rel3 = float((eng3.params - p20).abs().max() / p20.abs().max())
+    assert rel3 < 1e-4, ("host-fed fused vs resident fused", rel3)
+    assert np.abs(hl.numpy() - ref).max() < 1e-4 * np.abs(ref).max()
+    mine = eng3.params.clone()
+    other = mine.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(mine, other), "host-fed fused replicas diverged"
     dist.barrier()
     if rank == 0:
         print("MULTIGPU_OK world %d exchange %s act_exchange %s max loss err %.2e fused-vs-nccl %.2e" %

@@ -188,16 +188,22 @@ def test_checkpoint_roundtrip(dev, tmp_path, golden):
     assert torch.equal(eng.params, eng2.params)
 
 
-def test_multi_gpu_ddp_matches_reference_ws2(dev):
-    """2 ranks over NCCL vs the reference's 2-rank gloo run (tests/golden/traj_ws2.npz)."""
+@pytest.mark.parametrize("act_exchange", [True, False])
+def test_multi_gpu_ddp_matches_reference_ws2(dev, act_exchange):
+    """2 ranks vs the reference's 2-rank gloo run (tests/golden/traj_ws2.npz): NCCL between kernels, the fused
+    in-kernel exchange (with the dz1 activation exchange and with the plain bucket exchange) and the host-fed
+    fused loop (bit-identical to the resident fused loop under the plain bucket exchange)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import subprocess
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ)
+    if not act_exchange:
+        env["DDPM_NO_ACT_EXCHANGE"] = "1"
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                          "--master-addr", "127.0.0.1", "--master-port", "29733",
-                          os.path.join(here, "multigpu_check.py")], capture_output=True, text=True, timeout=600)
+                          "--master-addr", "127.0.0.1", "--master-port", "29733" if act_exchange else "29735",
+                          os.path.join(here, "multigpu_check.py")], capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "MULTIGPU_OK" in out.stdout
 
