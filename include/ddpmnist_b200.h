@@ -219,6 +219,49 @@ int  ddpm_train_steps_host_fed(ddpm_feed* feed, ddpm_comm* comm, float* d_params
                                int nsteps, unsigned flags, float lr,
                                float* d_loss, float* h_loss_steps, void* d_workspace, void* stream);
 
+/* -------------------------------------------------------------------------------- BASELINE.json "ConvNet"
+ * SURVEY.md §8(a) rows J1-J5.  NOT IN THE REFERENCE (the reference defines only the MLP
+ * above); these entry points implement the layer list BASELINE.json names behind the same boundary
+ * (resident u8 dataset + int64 sample indices in, loss out) and are checked against
+ * oracle/convnet_oracle.py, a restatement - parity unpinned.
+ *   conv1 1->32 3x3 + ReLU; conv2 32->64 3x3 + ReLU; max_pool2d(2); dropout(.25); flatten (c, y, x);
+ *   fc1 9216->128 + ReLU; dropout(.5); fc2 128->10; log_softmax; nll_loss (mean)        -- J1-J3
+ *   backward of all of it into one flat gradient bucket (4,799,528 B)                   -- J4
+ *   Adadelta (lr 1.0, rho 0.9, eps 1e-6), one fused pass over the flat arrays           -- J5
+ * Flat parameter layout = state_dict order: conv1.weight [32,1,3,3], conv1.bias, conv2.weight
+ * [64,32,3,3], conv2.bias, fc1.weight [128,9216], fc1.bias, fc2.weight [10,128], fc2.bias. */
+#define DDPM_CN_N_PARAMS     1199882
+#define DDPM_CN_OFF_CONV1_W  0
+#define DDPM_CN_OFF_CONV1_B  288
+#define DDPM_CN_OFF_CONV2_W  320
+#define DDPM_CN_OFF_CONV2_B  18752
+#define DDPM_CN_OFF_FC1_W    18816
+#define DDPM_CN_OFF_FC1_B    1198464
+#define DDPM_CN_OFF_FC2_W    1198592
+#define DDPM_CN_OFF_FC2_B    1199872
+#define DDPM_CN_MAX_BATCH    8192
+size_t ddpm_cn_workspace_bytes(int max_batch);               /* 0 if max_batch is out of range; ~370 KB per image */
+int ddpm_cn_workspace_init(void* d_workspace, int max_batch, void* stream);
+/* Forward (+ loss).  d_mask1 u8[batch][9216] / d_mask2 u8[batch][128]: injected dropout keep masks
+ * (both or neither); DDPM_FWD_PHILOX_MASK: masks from Philox4x32-10 at (seed, step); neither: eval
+ * mode.  DDPM_FWD_PREP_BACKWARD keeps what ddpm_cn_step_backward needs.  d_logprobs f32[batch][10]
+ * or NULL; d_loss f32[2] as in ddpm_step_forward. */
+int ddpm_cn_step_forward(const float* d_params,
+                         const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
+                         const int64_t* d_idx, const uint8_t* d_mask1, const uint8_t* d_mask2,
+                         uint64_t philox_seed, uint64_t philox_step, int batch, unsigned flags,
+                         float* d_logprobs, float* d_loss, void* d_workspace, void* stream);
+/* Backward of the step whose forward just ran with DDPM_FWD_PREP_BACKWARD on the same workspace:
+ * d_grads f32[1199882] = grad_scale x gradient of the mean loss (grad_scale = 1/world_size under
+ * data parallelism, then allreduce(SUM) the bucket).  train: the forward's mode (1 = with dropout). */
+int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_images, int64_t n_samples,
+                          const int64_t* d_idx, int batch, int train, float grad_scale,
+                          float* d_grads, void* d_workspace, void* stream);
+/* torch.optim.Adadelta's update on flat arrays (square_avg and acc_delta start at zero); the gradient
+ * is multiplied by grad_scale first.  Every operation individually rounded as on the CPU. */
+int ddpm_adadelta_step(float* d_params, const float* d_grads, float* d_square_avg, float* d_acc_delta,
+                       int64_t n, float lr, double rho, double eps, float grad_scale, void* stream);
+
 /* Forward/eval step for callers that cannot allocate.  No counterpart in the reference (added for
  * embedding; the reference is a script that allocates freely through torch).
  *

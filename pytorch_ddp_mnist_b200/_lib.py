@@ -19,7 +19,8 @@ FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
 BWD_TF32 = 1
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
-ABI_VERSION = 4
+CN_N_PARAMS, CN_MAX_BATCH = 1199882, 8192
+ABI_VERSION = 5
 
 
 class DDPMError(RuntimeError):
@@ -64,6 +65,11 @@ SIGNATURES = {
     "ddpm_feed_error": (_i32, [_vp, C.POINTER(_i32)]),
     "ddpm_feed_destroy": (None, [_vp]),
     "ddpm_train_steps_host_fed": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _u64, _i32, _u32, _f32, _vp, _vp, _vp, _vp]),
+    "ddpm_cn_workspace_bytes": (C.c_size_t, [_i32]),
+    "ddpm_cn_workspace_init": (_i32, [_vp, _i32, _vp]),
+    "ddpm_cn_step_forward": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _u64, _u64, _i32, _u32, _vp, _vp, _vp, _vp]),
+    "ddpm_cn_step_backward": (_i32, [_vp, _vp, _i64, _vp, _i32, _i32, _f32, _vp, _vp, _vp]),
+    "ddpm_adadelta_step": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, C.c_double, C.c_double, _f32, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _u32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),
     "ddpm_sgd_step": (_i32, [_vp, _vp, _i64, _f32, _f32, _vp]),

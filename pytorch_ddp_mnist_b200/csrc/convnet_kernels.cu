@@ -1,0 +1,755 @@
+// BASELINE.json's "ConvNet"  behind the same boundary as the reference's MLP:
+//   conv 1->32 3x3 + ReLU | conv 32->64 3x3 + ReLU + maxpool 2 + dropout .25 + flatten |
+//   fc 9216->128 + ReLU + dropout .5 | fc 128->10 | log_softmax + nll_loss | backward | Adadelta
+// The model is NOT in the reference: the checker is oracle/convnet_oracle.py, a restatement of
+// BASELINE.json's layer list - "parity unpinned".  Same input path as the MLP: resident u8 dataset, int64
+// sample indices, decode through the 256-entry table.
+//
+// fp32 FFMA throughout, fixed summation order (no atomics on data).  One CTA works on one image (x one half of
+// the channels) with the image's activations in shared memory:
+//   cn_conv1_kernel      x (gathered, decoded) -> a1 [B][32][26x26]                               (J1)
+//   cn_conv2_pool_kernel a1 -> conv2 + bias + ReLU + 2x2 max + dropout -> p2d [B][9216], flags    (J2)
+//   cn_fc1_fwd_kernel    split-K partials of p2d . Wfc1^T                                         (J3)
+//   cn_head_kernel       partial sums + bias + ReLU + dropout, fc2, log_softmax, nll, dlogits, dz(fc1)
+//   cn_fc1_bwd_kernel    dWfc1 tile + gradient of the pooled activations                          (J4)
+//   cn_conv2_dgrad_kernel / cn_conv2_wgrad_kernel / cn_conv1_bwd_kernel, cn_reduce_kernel
+//   adadelta_kernel      flat fused Adadelta                                                      (J5)
+#include "common.cuh"
+
+namespace ddpm {
+
+constexpr int C1 = 32, C2 = 64, H1 = 26, H2 = 24, HP = 12;
+constexpr int A1 = H1 * H1;                    // 676 conv1 outputs per channel
+constexpr int A1S = A1 + 1;                    // padded channel stride in shared memory (677: odd -> lanes = channels hit 32 banks)
+constexpr int NPOOL = HP * HP;                 // 144
+constexpr int FEAT = C2 * NPOOL;               // 9216
+constexpr int FC = 128;
+constexpr int OFF_C1W = DDPM_CN_OFF_CONV1_W, OFF_C1B = DDPM_CN_OFF_CONV1_B, OFF_C2W = DDPM_CN_OFF_CONV2_W,
+              OFF_C2B = DDPM_CN_OFF_CONV2_B, OFF_F1W = DDPM_CN_OFF_FC1_W, OFF_F1B = DDPM_CN_OFF_FC1_B,
+              OFF_F2W = DDPM_CN_OFF_FC2_W, OFF_F2B = DDPM_CN_OFF_FC2_B;
+constexpr int CONV_GRADS = OFF_F1W;            // 18,816 conv1 + conv2 gradient elements come as per-image partials
+constexpr int KSPLIT = FEAT / 128;             // 72 split-K slices of fc1
+constexpr uint32_t KEEP1_THR = 3221225472u;    // 0.75 * 2^32
+constexpr uint32_t KEEP2_THR = 2147483648u;    // 0.5  * 2^32
+constexpr float SCALE1 = 1.0f / 0.75f, SCALE2 = 2.0f;
+// pooled-activation flags (one byte per pooled element)
+constexpr unsigned PF_PASS = 4u;               // bits 0-1: argmax inside the 2x2 window (dy*2+dx); bit 2: gradient passes (value > 0 and kept)
+
+struct CnLayout {
+    size_t ctrl, a1, p2d, pflag, part, hd, dzf, dlog, rowloss, yb, dp2, dz1, gpart, total;
+};
+static CnLayout cn_layout(int B) {
+    CnLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    L.ctrl = take(256);
+    L.a1 = take((size_t)B * C1 * A1 * 4);
+    L.p2d = take((size_t)B * FEAT * 4);
+    L.pflag = take((size_t)B * FEAT);
+    L.part = take((size_t)KSPLIT * B * FC * 4);
+    L.hd = take((size_t)B * FC * 4);
+    L.dzf = take((size_t)B * FC * 4);
+    L.dlog = take((size_t)B * NCP * 4);
+    L.rowloss = take((size_t)B * 4);
+    L.yb = take((size_t)B);
+    L.dp2 = take((size_t)B * FEAT * 4);
+    L.dz1 = take((size_t)B * C1 * A1 * 4);
+    L.gpart = take((size_t)B * CONV_GRADS * 4);
+    L.total = o;
+    return L;
+}
+
+__host__ __device__ inline bool philox_keep_thr(uint64_t seed, uint64_t step, uint32_t elem, uint32_t thr) {
+    uint32_t r[4];
+    Philox::gen(seed, step, elem >> 2, r);
+    return r[elem & 3] < thr;
+}
+
+// ------------------------------------------------------------------------------------------ J1: conv1 + ReLU
+// grid = B, 256 threads.  The 28x28 image is gathered through idx and decoded through the table into shared memory.
+__global__ void __launch_bounds__(256)
+cn_conv1_kernel(const float* __restrict__ params, const uint8_t* __restrict__ images, int64_t n_samples,
+                const int64_t* __restrict__ idx, float* __restrict__ a1) {
+    __shared__ float xs[IN];
+    __shared__ float ws[C1 * 9 + C1];
+    __shared__ float lut[256];
+    const int tid = threadIdx.x, b = blockIdx.x;
+    lut[tid] = decode_px(tid);
+    for (int t = tid; t < C1 * 9 + C1; t += 256) ws[t] = params[OFF_C1W + t];     // weights [32][9] then bias [32]
+    __syncthreads();
+    const int64_t s = idx[b];
+    const bool ok = s >= 0 && s < n_samples;
+    for (int t = tid; t < IN / 4; t += 256) {
+        const uint32_t v = ok ? __ldg(reinterpret_cast<const uint32_t*>(images + s * IN) + t) : 0u;
+        xs[t * 4 + 0] = ok ? lut[v & 0xff] : 0.f;          xs[t * 4 + 1] = ok ? lut[(v >> 8) & 0xff] : 0.f;
+        xs[t * 4 + 2] = ok ? lut[(v >> 16) & 0xff] : 0.f;  xs[t * 4 + 3] = ok ? lut[v >> 24] : 0.f;
+    }
+    __syncthreads();
+    float* out = a1 + (size_t)b * C1 * A1;
+    for (int o = tid; o < C1 * A1; o += 256) {
+        const int c = o / A1, pos = o - c * A1, y = pos / H1, x = pos - y * H1;
+        float acc = ws[C1 * 9 + c];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) acc = fmaf(xs[(y + ky) * 28 + x + kx], ws[c * 9 + ky * 3 + kx], acc);
+        out[o] = fmaxf(acc, 0.f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ J2: conv2 + ReLU + pool + dropout
+// grid = (B, 2): CTA (b, h) computes output channels [32h, 32h+32) of image b.  288 threads: thread -> (pooled
+// position p, group parity); each round it owns one 2x2 pooling window x 8 output channels = 32 accumulators, fed
+// from a 4x4 input patch per input channel (8 LDS.64) and 9 x 8 weights (18 LDS.128, warp-broadcast).
+constexpr int C2_THREADS = 288;
+constexpr size_t C2_SMEM = (size_t)(C1 * A1S + 288 * 32 + 32) * 4;         // a1 image + weights [ci*9+tap][32 co] + bias
+__global__ void __launch_bounds__(C2_THREADS, 1)
+cn_conv2_pool_kernel(const float* __restrict__ params, const float* __restrict__ a1, const uint8_t* __restrict__ mask1,
+                     uint64_t seed, uint64_t step, int use_philox, int train,
+                     float* __restrict__ p2d, uint8_t* __restrict__ pflag) {
+    extern __shared__ __align__(16) float sm[];
+    float* a1s = sm;                          // [32][677]
+    float* w2s = a1s + C1 * A1S;              // [288][32]
+    float* b2s = w2s + 288 * 32;
+    const int tid = threadIdx.x, b = blockIdx.x, half = blockIdx.y;
+    const float* src = a1 + (size_t)b * C1 * A1;
+    for (int t = tid; t < C1 * A1; t += C2_THREADS) {
+        const int c = t / A1, pos = t - c * A1;
+        a1s[c * A1S + pos] = src[t];
+    }
+    // conv2.weight is [co][ci][3][3]: element (co, r) with r = ci*9+tap sits at co*288 + r; transposed here to [r][co]
+    // (groups of 4 channels XOR-swizzled by r so that this transposing store is 4-way, not 32-way, bank-conflicted)
+    for (int t = tid; t < 288 * 32; t += C2_THREADS) {
+        const int co = t / 288, r = t - co * 288;
+        w2s[r * 32 + (((co >> 2) ^ (r & 7)) << 2) + (co & 3)] = params[OFF_C2W + (size_t)(half * 32 + co) * 288 + r];
+    }
+    if (tid < 32) b2s[tid] = params[OFF_C2B + half * 32 + tid];
+    __syncthreads();
+    const int p = tid % NPOOL, gh = tid / NPOOL;            // gh in {0, 1}
+    const int py = p / HP, px = p - py * HP;
+    for (int round = 0; round < 2; ++round) {
+        const int co0 = (gh + 2 * round) * 8;               // 8 output channels of this half
+        float acc[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[q][j] = 0.f;
+        for (int ci = 0; ci < C1; ++ci) {
+            float patch[4][4];
+            const float* base = a1s + ci * A1S + (2 * py) * H1 + 2 * px;
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) patch[r][c] = base[r * H1 + c];
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 3; ++kx) {
+                    const int r = ci * 9 + ky * 3 + kx;
+                    const float4 w0 = *reinterpret_cast<const float4*>(&w2s[r * 32 + ((((co0 >> 2)) ^ (r & 7)) << 2)]);
+                    const float4 w1 = *reinterpret_cast<const float4*>(&w2s[r * 32 + ((((co0 >> 2) + 1) ^ (r & 7)) << 2)]);
+                    const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+                        for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                acc[dy * 2 + dx][j] = fmaf(patch[dy + ky][dx + kx], w[j], acc[dy * 2 + dx][j]);
+                }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int co = half * 32 + co0 + j;
+            const float bias = b2s[co0 + j];
+            float m = acc[0][j] + bias;
+            unsigned arg = 0;
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+                const float v = acc[q][j] + bias;
+                if (v > m) { m = v; arg = q; }              // first maximum wins, like max_pool2d's window scan
+            }
+            const size_t e = (size_t)b * FEAT + (size_t)co * NPOOL + p;
+            bool keep = true;
+            if (train) keep = use_philox ? philox_keep_thr(seed, step, (uint32_t)e, KEEP1_THR) : (mask1[e] != 0);
+            const bool pos = m > 0.f;
+            p2d[e] = (pos && keep) ? (train ? m * SCALE1 : m) : 0.f;
+            pflag[e] = (uint8_t)(arg | ((pos && keep) ? PF_PASS : 0u));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ J3: fc1 forward, split-K
+// grid = 72 (slices of 128 features), 256 threads.  part[ks][b][n] = sum_{k in slice} p2d[b][k] . W[n][k].
+// W slice transposed into Ws[k][n] (stride 129), rows in chunks of 64: thread tile 4 rows x 8 units.
+constexpr int F1_LD = 129;
+constexpr size_t F1_SMEM = (size_t)(128 * F1_LD + 64 * F1_LD) * 4;
+__global__ void __launch_bounds__(256, 1)
+cn_fc1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ p2d, int B, float* __restrict__ part) {
+    extern __shared__ __align__(16) float sm[];
+    float* Ws = sm;                           // [k][n] stride 129
+    float* Xs = Ws + 128 * F1_LD;             // [row][k] stride 129
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, ks = blockIdx.x, k0 = ks * 128;
+    for (int seg = warp; seg < 128 * 4; seg += 8) {          // (unit n, 32 consecutive k): coalesced read, conflict-free write
+        const int n = seg >> 2, kk = (seg & 3) * 32 + lane;
+        Ws[kk * F1_LD + n] = params[OFF_F1W + (size_t)n * FEAT + k0 + kk];
+    }
+    const int tn = tid & 15, rg = tid >> 4;
+    for (int r0 = 0; r0 < B; r0 += 64) {
+        __syncthreads();
+        for (int seg = warp; seg < 64 * 4; seg += 8) {
+            const int r = seg >> 2, kk = (seg & 3) * 32 + lane;
+            Xs[r * F1_LD + kk] = (r0 + r < B) ? p2d[(size_t)(r0 + r) * FEAT + k0 + kk] : 0.f;
+        }
+        __syncthreads();
+        float acc[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < 128; ++k) {
+            float x[4], w[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[i] = Xs[(rg * 4 + i) * F1_LD + k];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = Ws[k * F1_LD + tn + 16 * j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(x[i], w[j], acc[i][j]);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = r0 + rg * 4 + i;
+            if (row < B)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) part[((size_t)ks * B + row) * FC + tn + 16 * j] = acc[i][j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ head: fc1 epilogue .. dz(fc1)
+// grid = B (one batch row per CTA), 128 threads (thread = fc1 unit).  Sum of the 72 split-K partials in slice order
+// + bias, ReLU, dropout(.5); fc2 + bias; log_softmax; nll (mean over the batch); dlogits = (softmax - onehot)/B;
+// gradient of fc1's pre-activation.  The last CTA to finish sums the per-row losses in row order.
+__global__ void __launch_bounds__(FC)
+cn_head_kernel(const float* __restrict__ params, const float* __restrict__ part, const uint8_t* __restrict__ labels,
+               int64_t n_samples, const int64_t* __restrict__ idx, const uint8_t* __restrict__ mask2,
+               uint64_t seed, uint64_t step, int use_philox, int train, int prep_backward, int B,
+               float* __restrict__ hd, float* __restrict__ dzf, float* __restrict__ dlog, float* __restrict__ logprobs,
+               float* __restrict__ rowloss, uint8_t* __restrict__ yb, float* __restrict__ loss2, uint32_t* __restrict__ ctrl) {
+    __shared__ float hs[FC];
+    __shared__ float zs[NCP], dzs[NCP];
+    __shared__ int last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, b = blockIdx.x;
+    float z = 0.f;
+    for (int ks = 0; ks < KSPLIT; ++ks) z += part[((size_t)ks * B + b) * FC + tid];
+    z += params[OFF_F1B + tid];
+    const bool pos = z > 0.f;
+    bool keep = true;
+    if (train) keep = use_philox ? philox_keep_thr(seed, step + (1ull << 62), (uint32_t)(b * FC + tid), KEEP2_THR)
+                                 : (mask2[(size_t)b * FC + tid] != 0);
+    const float h = (pos && keep) ? (train ? z * SCALE2 : z) : 0.f;
+    hs[tid] = h;
+    if (prep_backward) hd[(size_t)b * FC + tid] = h;
+    __syncthreads();
+    for (int c = warp; c < NC; c += FC / 32) {             // fc2: one warp per class
+        float v = 0.f;
+#pragma unroll
+        for (int k = 0; k < FC / 32; ++k) v = fmaf(hs[lane + 32 * k], params[OFF_F2W + c * FC + lane + 32 * k], v);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) zs[c] = v + params[OFF_F2B + c];
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const int64_t s = idx[b];
+        const int y = (s >= 0 && s < n_samples) ? labels[s] : 0;
+        const float v = lane < NC ? zs[lane] : -INFINITY;
+        float m = v;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        const float e = lane < NC ? expf(v - m) : 0.f;
+        float sum = e;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        const float lse = m + logf(sum);
+        const float lp = v - lse;
+        if (lane < NC && logprobs) logprobs[(size_t)b * NC + lane] = lp;
+        const float ly = __shfl_sync(0xffffffffu, lp, y);
+        if (lane == 0) { rowloss[b] = -ly; yb[b] = (uint8_t)y; }
+        if (lane < NCP) {
+            const float d = lane < NC ? (e / sum - (lane == y ? 1.f : 0.f)) / (float)B : 0.f;
+            dzs[lane] = d;
+            if (prep_backward) dlog[(size_t)b * NCP + lane] = d;
+        }
+    }
+    __syncthreads();
+    if (prep_backward) {
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) d = fmaf(dzs[c], params[OFF_F2W + c * FC + tid], d);
+        dzf[(size_t)b * FC + tid] = (pos && keep) ? (train ? d * SCALE2 : d) : 0.f;
+    }
+    // batch loss: the last CTA sums the rows in order
+    __threadfence();
+    if (tid == 0) last = (atomicAdd(&ctrl[0], 1u) == (unsigned)(B - 1));
+    __syncthreads();
+    if (last && warp == 0) {
+        __threadfence();
+        float v = 0.f;
+        for (int r0 = 0; r0 < B; r0 += 32) {
+            float x = (r0 + lane < B) ? __ldcg(rowloss + r0 + lane) : 0.f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+            v += x;
+        }
+        if (lane == 0) {
+            const float mean = v / (float)B;
+            if (loss2) { loss2[0] = mean; loss2[1] += mean / (float)B; }
+            ctrl[0] = 0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ J4: fc1 backward
+// grid = 72 feature tiles of 128, 256 threads.  CTA kt owns columns [128kt, 128kt+128) of fc1.weight:
+//   dW[n][k] = scale . sum_b dzf[b][n] . p2d[b][k]      (complete: every row of the batch passes through this CTA)
+//   g[b][k]  = sum_n dzf[b][n] . W[n][k], passed through the pooled element's flag (ReLU > 0 and kept) x 1/0.75
+// Rows in chunks of 64; dW accumulates in registers (8 x 8 per thread) across chunks.
+constexpr size_t F1B_SMEM = (size_t)(128 * F1_LD + 64 * 128 + 64 * 128) * 4;
+__global__ void __launch_bounds__(256, 1)
+cn_fc1_bwd_kernel(const float* __restrict__ params, const float* __restrict__ p2d, const uint8_t* __restrict__ pflag,
+                  const float* __restrict__ dzf, int B, int train, float scale, float* __restrict__ grads,
+                  float* __restrict__ dp2) {
+    extern __shared__ __align__(16) float sm[];
+    float* Ws = sm;                           // [n][k] stride 129
+    float* Ds = Ws + 128 * F1_LD;             // [row][n]
+    float* Xs = Ds + 64 * 128;                // [row][k]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, k0 = blockIdx.x * 128;
+    for (int seg = warp; seg < 128 * 4; seg += 8) {
+        const int n = seg >> 2, kk = (seg & 3) * 32 + lane;
+        Ws[n * F1_LD + kk] = params[OFF_F1W + (size_t)n * FEAT + k0 + kk];
+    }
+    const int tk = tid & 15, tn = tid >> 4;                 // dW tile: units tn + 16 i, columns tk + 16 j
+    float dw[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+    for (int r0 = 0; r0 < B; r0 += 64) {
+        __syncthreads();
+        for (int t = tid; t < 64 * 128; t += 256) {
+            const int r = t >> 7, c = t & 127;
+            const bool ok = r0 + r < B;
+            Ds[t] = ok ? dzf[(size_t)(r0 + r) * FC + c] : 0.f;
+            Xs[t] = ok ? p2d[(size_t)(r0 + r) * FEAT + k0 + c] : 0.f;
+        }
+        __syncthreads();
+        for (int r = 0; r < 64; ++r) {
+            float d[8], x[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d[i] = Ds[r * 128 + tn + 16 * i];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) x[j] = Xs[r * 128 + tk + 16 * j];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) dw[i][j] = fmaf(d[i], x[j], dw[i][j]);
+        }
+        // gradient of the pooled activations of these 64 rows: thread -> rows rg*4.., columns tk + 16 j
+        const int rg = tid >> 4;
+        float acc[4][8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 2
+        for (int n = 0; n < FC; ++n) {
+            float d[4], w[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) d[i] = Ds[(rg * 4 + i) * 128 + n];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = Ws[n * F1_LD + tk + 16 * j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(d[i], w[j], acc[i][j]);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = r0 + rg * 4 + i;
+            if (row < B)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const size_t e = (size_t)row * FEAT + k0 + tk + 16 * j;
+                    const bool pass = (pflag[e] & PF_PASS) != 0;
+                    dp2[e] = pass ? (train ? acc[i][j] * SCALE1 : acc[i][j]) : 0.f;
+                }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            grads[OFF_F1W + (size_t)(tn + 16 * i) * FEAT + k0 + tk + 16 * j] = dw[i][j] * scale;
+}
+
+// ------------------------------------------------------------------------------------------ J4: conv2 backward
+// The gradient reaching conv2's pre-activation is sparse: of each 2x2 window only the argmax element gets the pooled
+// gradient g (and only if its value was > 0 and it was kept by the dropout).  Both kernels rebuild a dense, zero-
+// filled dz2 plane set in shared memory from (g, flags) and then run a dense register-tiled product over it.
+
+// data gradient: da1[ci][y][x] = sum_{co,ky,kx} dz2[co][y-ky][x-kx] . W[co][ci][ky][kx]; dz1 = da1 . (a1 > 0).
+// grid = (B, 2): CTA (b, h) produces input channels [16h, 16h+16).  dz2 is held with a 2-wide zero border
+// ([32 co][28x28], two passes over the output-channel halves).  352 threads, 338 active: thread -> (2x2 window of
+// the 26x26 plane, 8 input channels).
+constexpr int DG_THREADS = 352;
+constexpr size_t DG_SMEM = (size_t)(32 * 784 + 32 * 9 * 16) * 4;
+__global__ void __launch_bounds__(DG_THREADS, 1)
+cn_conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ a1, const float* __restrict__ dp2,
+                      const uint8_t* __restrict__ pflag, float* __restrict__ dz1) {
+    extern __shared__ __align__(16) float sm[];
+    float* dzs = sm;                          // [32][28*28] zero-bordered
+    float* wsm = dzs + 32 * 784;              // [co 32][tap 9][ci 16]
+    const int tid = threadIdx.x, b = blockIdx.x, half = blockIdx.y;
+    const bool active = tid < 338;
+    const int w = tid % 169, cg = (tid / 169) & 1;
+    const int wy = w / 13, wx = w - wy * 13;
+    float acc[4][8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[q][j] = 0.f;
+    for (int hh = 0; hh < 2; ++hh) {
+        __syncthreads();
+        for (int t = tid; t < 32 * 784; t += DG_THREADS) dzs[t] = 0.f;
+        for (int t = tid; t < 32 * 9 * 16; t += DG_THREADS) {
+            const int ci = t & 15, tap = (t >> 4) % 9, co = t / 144;
+            wsm[t] = params[OFF_C2W + ((size_t)(hh * 32 + co) * C1 + half * 16 + ci) * 9 + tap];
+        }
+        __syncthreads();
+        for (int t = tid; t < 32 * NPOOL; t += DG_THREADS) {
+            const int co = t / NPOOL, p = t - co * NPOOL, py = p / HP, px = p - py * HP;
+            const size_t e = (size_t)b * FEAT + (size_t)(hh * 32 + co) * NPOOL + p;
+            const unsigned f = pflag[e];
+            if (f & PF_PASS) {
+                const int yo = 2 * py + ((f >> 1) & 1), xo = 2 * px + (f & 1);
+                dzs[co * 784 + (yo + 2) * 28 + xo + 2] = dp2[e];
+            }
+        }
+        __syncthreads();
+        if (active) {
+            for (int co = 0; co < 32; ++co) {
+                float patch[4][4];
+                const float* base = dzs + co * 784 + (2 * wy) * 28 + 2 * wx;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) patch[r][c] = base[r * 28 + c];
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        const float4 w0 = *reinterpret_cast<const float4*>(&wsm[((co * 9) + ky * 3 + kx) * 16 + cg * 8]);
+                        const float4 w1 = *reinterpret_cast<const float4*>(&wsm[((co * 9) + ky * 3 + kx) * 16 + cg * 8 + 4]);
+                        const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                        for (int r = 0; r < 2; ++r)
+#pragma unroll
+                            for (int c = 0; c < 2; ++c)
+#pragma unroll
+                                for (int j = 0; j < 8; ++j)
+                                    acc[r * 2 + c][j] = fmaf(patch[r - ky + 2][c - kx + 2], wv[j], acc[r * 2 + c][j]);
+                    }
+            }
+        }
+    }
+    if (active) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int ci = half * 16 + cg * 8 + j;
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const size_t e = ((size_t)b * C1 + ci) * A1 + (2 * wy + r) * H1 + 2 * wx + c;
+                    dz1[e] = a1[e] > 0.f ? acc[r * 2 + c][j] : 0.f;
+                }
+        }
+    }
+}
+
+// weight gradient of one image: dW2[co][ci][tap] = sum_pos dz2[co][pos] . a1[ci][pos + tap], db2[co] = sum_pos dz2.
+// grid = (B, 2): CTA (b, h) produces output channels [32h, 32h+32) into this image's partial-gradient row.
+// 256 threads: thread -> (input channel = lane, 8 output channels = warp & 3, half of the rows = warp >> 2):
+// 72 accumulators; walking a row it keeps the 3x3 input window in registers and loads 3 new values per step.
+constexpr size_t WG_SMEM = (size_t)(C1 * A1S + 32 * 576) * 4;
+__global__ void __launch_bounds__(256, 1)
+cn_conv2_wgrad_kernel(const float* __restrict__ a1, const float* __restrict__ dp2, const uint8_t* __restrict__ pflag,
+                      float* __restrict__ gpart) {
+    extern __shared__ __align__(16) float sm[];
+    float* a1s = sm;                          // [32][677]
+    float* dzd = a1s + C1 * A1S;              // [32 co][24*24] dense
+    const int tid = threadIdx.x, b = blockIdx.x, half = blockIdx.y;
+    const float* src = a1 + (size_t)b * C1 * A1;
+    for (int t = tid; t < C1 * A1; t += 256) {
+        const int c = t / A1, pos = t - c * A1;
+        a1s[c * A1S + pos] = src[t];
+    }
+    for (int t = tid; t < 32 * 576; t += 256) dzd[t] = 0.f;
+    __syncthreads();
+    for (int t = tid; t < 32 * NPOOL; t += 256) {
+        const int co = t / NPOOL, p = t - co * NPOOL, py = p / HP, px = p - py * HP;
+        const size_t e = (size_t)b * FEAT + (size_t)(half * 32 + co) * NPOOL + p;
+        const unsigned f = pflag[e];
+        if (f & PF_PASS) dzd[co * 576 + (2 * py + ((f >> 1) & 1)) * H2 + 2 * px + (f & 1)] = dp2[e];
+    }
+    __syncthreads();
+    float* grow = gpart + (size_t)b * CONV_GRADS;
+    if (tid < 32) {                                          // db2: the 144 pooled gradients of the channel, in order
+        float v = 0.f;
+        for (int pos = 0; pos < 576; ++pos) v += dzd[tid * 576 + pos];
+        grow[OFF_C2B + half * 32 + tid] = v;
+    }
+    const int ci = tid & 31, oct = (tid >> 5) & 3, ph = tid >> 7;
+    float acc[8][9];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc[j][t] = 0.f;
+    const float* ap = a1s + ci * A1S;
+    for (int yo = ph * 12; yo < ph * 12 + 12; ++yo) {
+        float win[3][3];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) { win[ky][1] = ap[(yo + ky) * H1]; win[ky][2] = ap[(yo + ky) * H1 + 1]; }
+        for (int xo = 0; xo < H2; ++xo) {
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+                win[ky][0] = win[ky][1]; win[ky][1] = win[ky][2]; win[ky][2] = ap[(yo + ky) * H1 + xo + 2];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float d = dzd[(oct * 8 + j) * 576 + yo * H2 + xo];
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) acc[j][ky * 3 + kx] = fmaf(d, win[ky][kx], acc[j][ky * 3 + kx]);
+            }
+        }
+    }
+    __syncthreads();                                         // everyone is done with dzd: reuse it to combine the halves
+    if (ph == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+            for (int t = 0; t < 9; ++t) dzd[(j * 9 + t) * 128 + (tid & 127)] = acc[j][t];
+    }
+    __syncthreads();
+    if (ph == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int co = half * 32 + oct * 8 + j;
+#pragma unroll
+            for (int t = 0; t < 9; ++t)
+                grow[OFF_C2W + ((size_t)co * C1 + ci) * 9 + t] = acc[j][t] + dzd[(j * 9 + t) * 128 + tid];
+        }
+    }
+}
+
+// conv1's weight gradient of one image: dW1[c][tap] = sum_pos dz1[c][pos] . x[pos + tap], db1[c] = sum_pos dz1[c][pos]
+// (conv1's input needs no gradient).  grid = B, 320 threads: 288 (channel, tap) pairs + 32 bias sums.
+constexpr size_t C1B_SMEM = (size_t)(C1 * A1S + IN + 256) * 4;
+__global__ void __launch_bounds__(320, 1)
+cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const int64_t* __restrict__ idx,
+                    const float* __restrict__ dz1, float* __restrict__ gpart) {
+    extern __shared__ __align__(16) float sm[];
+    float* dzs = sm;                          // [32][677]
+    float* xs = dzs + C1 * A1S;               // [28*28]
+    float* lut = xs + IN;
+    const int tid = threadIdx.x, b = blockIdx.x;
+    if (tid < 256) lut[tid] = decode_px(tid);
+    const float* src = dz1 + (size_t)b * C1 * A1;
+    for (int t = tid; t < C1 * A1; t += 320) {
+        const int c = t / A1, pos = t - c * A1;
+        dzs[c * A1S + pos] = src[t];
+    }
+    __syncthreads();
+    const int64_t s = idx[b];
+    const bool ok = s >= 0 && s < n_samples;
+    for (int t = tid; t < IN; t += 320) xs[t] = ok ? lut[images[s * IN + t]] : 0.f;
+    __syncthreads();
+    float* grow = gpart + (size_t)b * CONV_GRADS;
+    if (tid < 288) {
+        const int c = tid / 9, tap = tid - c * 9, ky = tap / 3, kx = tap - ky * 3;
+        float v = 0.f;
+        for (int y = 0; y < H1; ++y)
+            for (int x = 0; x < H1; ++x) v = fmaf(dzs[c * A1S + y * H1 + x], xs[(y + ky) * 28 + x + kx], v);
+        grow[OFF_C1W + tid] = v;
+    } else {
+        const int c = tid - 288;
+        float v = 0.f;
+        for (int pos = 0; pos < A1; ++pos) v += dzs[c * A1S + pos];
+        grow[OFF_C1B + c] = v;
+    }
+}
+
+// sum of the per-image partial gradients (fixed image order) and the three small gradients of the dense layers
+// (fc1.bias, fc2.weight, fc2.bias: sums over the batch of dzf, dlogits x hd, dlogits).
+constexpr int RED_BLOCKS = (CONV_GRADS + 255) / 256;       // 74
+constexpr int SMALL_N = FC + NC * FC + NC;                 // 1418
+constexpr int SMALL_BLOCKS = (SMALL_N + 255) / 256;        // 6
+__global__ void __launch_bounds__(256)
+cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf, const float* __restrict__ dlog,
+                 const float* __restrict__ hd, int B, float scale, float* __restrict__ grads) {
+    const int tid = threadIdx.x;
+    if (blockIdx.x < RED_BLOCKS) {
+        const int j = blockIdx.x * 256 + tid;
+        if (j >= CONV_GRADS) return;
+        float v = 0.f;
+        for (int b = 0; b < B; ++b) v += gpart[(size_t)b * CONV_GRADS + j];
+        grads[j] = v * scale;
+        return;
+    }
+    const int e = (blockIdx.x - RED_BLOCKS) * 256 + tid;
+    if (e >= SMALL_N) return;
+    float v = 0.f;
+    if (e < FC) {
+        for (int b = 0; b < B; ++b) v += dzf[(size_t)b * FC + e];
+        grads[OFF_F1B + e] = v * scale;
+    } else if (e < FC + NC * FC) {
+        const int c = (e - FC) / FC, n = (e - FC) - c * FC;
+        for (int b = 0; b < B; ++b) v = fmaf(dlog[(size_t)b * NCP + c], hd[(size_t)b * FC + n], v);
+        grads[OFF_F2W + c * FC + n] = v * scale;
+    } else {
+        const int c = e - FC - NC * FC;
+        for (int b = 0; b < B; ++b) v += dlog[(size_t)b * NCP + c];
+        grads[OFF_F2B + c] = v * scale;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ J5: Adadelta
+// torch.optim.Adadelta's single-tensor rule (torch/optim/adadelta.py:292-302), one pass over the flat arrays:
+//   sq <- rho sq + (1-rho) g g ; std = sqrt(sq + eps) ; delta = sqrt(acc + eps) / std . g ;
+//   acc <- rho acc + (1-rho) delta delta ; p <- p - lr delta
+// Every operation individually rounded (no contraction), as the CPU's vectorised elementwise kernels do.
+__global__ void __launch_bounds__(256)
+adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, float* __restrict__ acc,
+                int64_t n, float lr, float rho, float one_minus_rho, float eps, float gscale) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+        const float gv = __fmul_rn(g[i], gscale);
+        const float s = __fadd_rn(__fmul_rn(sq[i], rho), __fmul_rn(__fmul_rn(one_minus_rho, gv), gv));
+        const float std = __fsqrt_rn(__fadd_rn(s, eps));
+        const float delta = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(acc[i], eps)), std), gv);
+        const float a = __fadd_rn(__fmul_rn(acc[i], rho), __fmul_rn(__fmul_rn(one_minus_rho, delta), delta));
+        sq[i] = s; acc[i] = a;
+        p[i] = fmaf(-lr, delta, p[i]);
+    }
+}
+
+}  // namespace ddpm
+
+// ------------------------------------------------------------------------------------------ C ABI
+using namespace ddpm;
+
+static int cn_configure() {
+    static bool done[64] = {};
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !done[dev]) {
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C2_SMEM));
+        DDPM_CUDA(cudaFuncSetAttribute(cn_fc1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F1_SMEM));
+        DDPM_CUDA(cudaFuncSetAttribute(cn_fc1_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F1B_SMEM));
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DG_SMEM));
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WG_SMEM));
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv1_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C1B_SMEM));
+        done[dev] = true;
+    }
+    return 0;
+}
+
+extern "C" size_t ddpm_cn_workspace_bytes(int max_batch) {
+    if (max_batch <= 0 || max_batch > DDPM_CN_MAX_BATCH) return 0;
+    return cn_layout(max_batch).total;
+}
+
+extern "C" int ddpm_cn_workspace_init(void* d_workspace, int max_batch, void* stream) {
+    DDPM_CHECK_ARG(d_workspace != nullptr && max_batch > 0 && max_batch <= DDPM_CN_MAX_BATCH,
+                   "ddpm_cn_workspace_init: bad arguments (max_batch %d, limit %d)", max_batch, DDPM_CN_MAX_BATCH);
+    DDPM_CUDA(cudaMemsetAsync(d_workspace, 0, 256, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_images, const uint8_t* d_labels,
+                                    int64_t n_samples, const int64_t* d_idx, const uint8_t* d_mask1,
+                                    const uint8_t* d_mask2, uint64_t philox_seed, uint64_t philox_step, int batch,
+                                    unsigned flags, float* d_logprobs, float* d_loss, void* d_workspace, void* stream) {
+    const char* who = "ddpm_cn_step_forward";
+    DDPM_CHECK_ARG(batch > 0 && batch <= DDPM_CN_MAX_BATCH, "%s: batch %d outside [1, %d]", who, batch, DDPM_CN_MAX_BATCH);
+    DDPM_CHECK_ARG(d_params && d_images && d_labels && d_idx && d_workspace && n_samples > 0, "%s: null pointer or empty dataset", who);
+    DDPM_CHECK_ARG((flags & ~(DDPM_FWD_PREP_BACKWARD | DDPM_FWD_PHILOX_MASK)) == 0, "%s: unknown flags %#x", who, flags);
+    DDPM_CHECK_ARG((d_mask1 == nullptr) == (d_mask2 == nullptr), "%s: give both dropout masks or neither", who);
+    DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0 && ((uintptr_t)d_images & 3) == 0, "%s: misaligned pointer", who);
+    if (cn_configure()) return 1;
+    const bool philox = (flags & DDPM_FWD_PHILOX_MASK) != 0;
+    const int train = (philox || d_mask1 != nullptr) ? 1 : 0;
+    const int prep = (flags & DDPM_FWD_PREP_BACKWARD) ? 1 : 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)d_workspace;
+    const CnLayout L = cn_layout(batch);
+    float* a1 = (float*)(ws + L.a1);
+    float* p2d = (float*)(ws + L.p2d);
+    uint8_t* pflag = (uint8_t*)(ws + L.pflag);
+    float* part = (float*)(ws + L.part);
+    uint32_t* ctrl = (uint32_t*)(ws + L.ctrl);
+    cn_conv1_kernel<<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1);
+    cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
+                                                                    philox_step, philox ? 1 : 0, train, p2d, pflag);
+    cn_fc1_fwd_kernel<<<KSPLIT, 256, F1_SMEM, st>>>(d_params, p2d, batch, part);
+    cn_head_kernel<<<batch, FC, 0, st>>>(d_params, part, d_labels, n_samples, d_idx, philox ? nullptr : d_mask2, philox_seed,
+                                         philox_step, philox ? 1 : 0, train, prep, batch, (float*)(ws + L.hd),
+                                         (float*)(ws + L.dzf), (float*)(ws + L.dlog), d_logprobs, (float*)(ws + L.rowloss),
+                                         (uint8_t*)(ws + L.yb), d_loss, ctrl);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_images, int64_t n_samples,
+                                     const int64_t* d_idx, int batch, int train, float grad_scale, float* d_grads,
+                                     void* d_workspace, void* stream) {
+    const char* who = "ddpm_cn_step_backward";
+    DDPM_CHECK_ARG(batch > 0 && batch <= DDPM_CN_MAX_BATCH, "%s: batch %d outside [1, %d]", who, batch, DDPM_CN_MAX_BATCH);
+    DDPM_CHECK_ARG(d_params && d_images && d_idx && d_grads && d_workspace && n_samples > 0, "%s: null pointer or empty dataset", who);
+    DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0, "%s: misaligned workspace", who);
+    if (cn_configure()) return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)d_workspace;
+    const CnLayout L = cn_layout(batch);
+    float* a1 = (float*)(ws + L.a1);
+    float* p2d = (float*)(ws + L.p2d);
+    uint8_t* pflag = (uint8_t*)(ws + L.pflag);
+    float* dzf = (float*)(ws + L.dzf);
+    float* dp2 = (float*)(ws + L.dp2);
+    float* dz1 = (float*)(ws + L.dz1);
+    float* gpart = (float*)(ws + L.gpart);
+    cn_fc1_bwd_kernel<<<KSPLIT, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
+    cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
+    cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
+    cn_conv1_bwd_kernel<<<batch, 320, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
+    cn_reduce_kernel<<<RED_BLOCKS + SMALL_BLOCKS, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
+                                                               (const float*)(ws + L.hd), batch, grad_scale, d_grads);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ddpm_adadelta_step(float* d_params, const float* d_grads, float* d_square_avg, float* d_acc_delta,
+                                  int64_t n, float lr, double rho, double eps, float grad_scale, void* stream) {
+    DDPM_CHECK_ARG(d_params && d_grads && d_square_avg && d_acc_delta && n > 0, "ddpm_adadelta_step: null pointer or n <= 0");
+    const float one_minus_rho = (float)(1.0 - rho);          // torch forms 1 - rho in double, then rounds once
+    const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+    adadelta_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_params, d_grads, d_square_avg, d_acc_delta, n, lr, (float)rho,
+                                                              one_minus_rho, (float)eps, grad_scale);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}

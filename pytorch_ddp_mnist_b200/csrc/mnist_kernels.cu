@@ -1079,7 +1079,7 @@ extern "C" {
 
 const char* ddpm_last_error(void) { return g_err; }
 
-int ddpm_abi_version(void) { return 4; }
+int ddpm_abi_version(void) { return 5; }
 
 int ddpm_decode_lut_host(float* h_lut256) {
     DDPM_CHECK_ARG(h_lut256 != nullptr, "ddpm_decode_lut_host: null output");
