@@ -39,9 +39,11 @@ class ConvNetWorkspace:
 def step_forward(params: torch.Tensor, ws: ConvNetWorkspace, *, images: torch.Tensor, labels: torch.Tensor,
                  idx: torch.Tensor, mask1: Optional[torch.Tensor] = None, mask2: Optional[torch.Tensor] = None,
                  philox: Optional[Tuple[int, int]] = None, prep_backward: bool = False,
-                 logprobs: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None) -> None:
+                 logprobs: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None,
+                 tf32: bool = False) -> None:
     """conv1 .. nll_loss for the samples `idx` of the resident dataset.  Dropout: `mask1` u8[B,9216] +
-    `mask2` u8[B,128] (injected), or `philox=(seed, step)`, or neither = eval mode."""
+    `mask2` u8[B,128] (injected), or `philox=(seed, step)`, or neither = eval mode.  `tf32`: conv2 as an
+    implicit GEMM on the tcgen05 tensor cores (TF32 operands, fp32 accumulate; ~1e-3 relative)."""
     _need(params, "params", torch.float32, (CN_N_PARAMS,))
     _need(images, "images", torch.uint8)
     n = images.shape[0]
@@ -54,7 +56,8 @@ def step_forward(params: torch.Tensor, ws: ConvNetWorkspace, *, images: torch.Te
     _need(mask2, "mask2", torch.uint8, (b, FC), optional=True)
     _need(logprobs, "logprobs", torch.float32, (b, 10), optional=True)
     _need(loss, "loss", torch.float32, (2,), optional=True)
-    flags = (_lib.FWD_PREP_BACKWARD if prep_backward else 0) | (_lib.FWD_PHILOX_MASK if philox else 0)
+    flags = ((_lib.FWD_PREP_BACKWARD if prep_backward else 0) | (_lib.FWD_PHILOX_MASK if philox else 0)
+             | (_lib.FWD_TF32 if tf32 else 0))
     seed, step = philox if philox else (0, 0)
     check(lib.ddpm_cn_step_forward(ptr(params), ptr(images), ptr(labels), n, ptr(idx), ptr(mask1), ptr(mask2),
                                    seed, step, b, flags, ptr(logprobs), ptr(loss), ptr(ws.buf), cur_stream()))
@@ -86,8 +89,9 @@ class ConvNetEngine:
     """Flat-parameter training engine for the ConvNet: forward, backward into one bucket, (all-reduce), Adadelta."""
 
     def __init__(self, device, max_batch: int, lr: float = 1.0, rho: float = 0.9, eps: float = 1e-6,
-                 world_size: int = 1, rank: int = 0, group=None, seed: int = 42):
+                 world_size: int = 1, rank: int = 0, group=None, seed: int = 42, tf32: bool = False):
         self.device = torch.device(device)
+        self.tf32 = bool(tf32)
         self.lr, self.rho, self.eps = float(lr), float(rho), float(eps)
         self.world_size, self.rank, self.group = int(world_size), int(rank), group
         self.seed = int(seed) + 0x9E3779B97F4A7C15 * self.rank & 0xFFFFFFFFFFFFFFFF
@@ -128,7 +132,7 @@ class ConvNetEngine:
             kw = dict(mask1=mask1, mask2=mask2)
         self.step_count += 1
         step_forward(self.params, self.ws, images=resident.images, labels=resident.labels, idx=idx, prep_backward=True,
-                     loss=self.loss, **kw)
+                     loss=self.loss, tf32=self.tf32, **kw)
         step_backward(self.params, self.ws, self.grads, images=resident.images, idx=idx, train=True,
                       grad_scale=1.0 / self.world_size)
         if self.world_size > 1:

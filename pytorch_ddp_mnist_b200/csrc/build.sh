@@ -7,5 +7,5 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "${NVCC}" -shared -Xcompiler -fPIC -O3 -std=c++17 -lineinfo \
     -gencode arch=compute_100a,code=sm_100a \
     ${DDPM_PTXAS_V:+-Xptxas -v} ${DDPM_DEFS:-} \
-    -o "${OUT}" "${HERE}/mnist_kernels.cu" "${HERE}/persist_kernel.cu" "${HERE}/fc1_tc.cu" "${HERE}/convnet_kernels.cu" "${HERE}/cdf5_reader.cpp" ${DDPM_EXTRA_SRC:-} -lcudart
+    -o "${OUT}" "${HERE}/mnist_kernels.cu" "${HERE}/persist_kernel.cu" "${HERE}/fc1_tc.cu" "${HERE}/convnet_kernels.cu" "${HERE}/convnet_tc.cu" "${HERE}/cdf5_reader.cpp" ${DDPM_EXTRA_SRC:-} -lcudart
 echo "built ${OUT}"

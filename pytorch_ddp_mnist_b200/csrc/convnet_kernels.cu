@@ -14,68 +14,27 @@
 //   cn_fc1_bwd_kernel    dWfc1 tile + gradient of the pooled activations                          (J4)
 //   cn_conv2_dgrad_kernel / cn_conv2_wgrad_kernel / cn_conv1_bwd_kernel, cn_reduce_kernel
 //   adadelta_kernel      flat fused Adadelta                                                      (J5)
-#include "common.cuh"
+#include "convnet.cuh"
 
 namespace ddpm {
 
-constexpr int C1 = 32, C2 = 64, H1 = 26, H2 = 24, HP = 12;
-constexpr int A1 = H1 * H1;                    // 676 conv1 outputs per channel
-constexpr int A1S = A1 + 1;                    // padded channel stride in shared memory (677: odd -> lanes = channels hit 32 banks)
-constexpr int NPOOL = HP * HP;                 // 144
-constexpr int FEAT = C2 * NPOOL;               // 9216
-constexpr int FC = 128;
-constexpr int OFF_C1W = DDPM_CN_OFF_CONV1_W, OFF_C1B = DDPM_CN_OFF_CONV1_B, OFF_C2W = DDPM_CN_OFF_CONV2_W,
-              OFF_C2B = DDPM_CN_OFF_CONV2_B, OFF_F1W = DDPM_CN_OFF_FC1_W, OFF_F1B = DDPM_CN_OFF_FC1_B,
-              OFF_F2W = DDPM_CN_OFF_FC2_W, OFF_F2B = DDPM_CN_OFF_FC2_B;
-constexpr int CONV_GRADS = OFF_F1W;            // 18,816 conv1 + conv2 gradient elements come as per-image partials
-constexpr int KSPLIT = FEAT / 128;             // 72 split-K slices of fc1
-constexpr uint32_t KEEP1_THR = 3221225472u;    // 0.75 * 2^32
-constexpr uint32_t KEEP2_THR = 2147483648u;    // 0.5  * 2^32
-constexpr float SCALE1 = 1.0f / 0.75f, SCALE2 = 2.0f;
-// pooled-activation flags (one byte per pooled element)
-constexpr unsigned PF_PASS = 4u;               // bits 0-1: argmax inside the 2x2 window (dy*2+dx); bit 2: gradient passes (value > 0 and kept)
-
-struct CnLayout {
-    size_t ctrl, a1, p2d, pflag, part, hd, dzf, dlog, rowloss, yb, dp2, dz1, gpart, total;
-};
-static CnLayout cn_layout(int B) {
-    CnLayout L;
-    size_t o = 0;
-    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
-    L.ctrl = take(256);
-    L.a1 = take((size_t)B * C1 * A1 * 4);
-    L.p2d = take((size_t)B * FEAT * 4);
-    L.pflag = take((size_t)B * FEAT);
-    L.part = take((size_t)KSPLIT * B * FC * 4);
-    L.hd = take((size_t)B * FC * 4);
-    L.dzf = take((size_t)B * FC * 4);
-    L.dlog = take((size_t)B * NCP * 4);
-    L.rowloss = take((size_t)B * 4);
-    L.yb = take((size_t)B);
-    L.dp2 = take((size_t)B * FEAT * 4);
-    L.dz1 = take((size_t)B * C1 * A1 * 4);
-    L.gpart = take((size_t)B * CONV_GRADS * 4);
-    L.total = o;
-    return L;
-}
-
-__host__ __device__ inline bool philox_keep_thr(uint64_t seed, uint64_t step, uint32_t elem, uint32_t thr) {
-    uint32_t r[4];
-    Philox::gen(seed, step, elem >> 2, r);
-    return r[elem & 3] < thr;
-}
-
 // ------------------------------------------------------------------------------------------ J1: conv1 + ReLU
-// grid = B, 256 threads.  The 28x28 image is gathered through idx and decoded through the table into shared memory.
+// grid = B, 256 threads.  The 28x28 image is gathered through idx and decoded through the table into shared memory;
+// a thread owns an output pixel: its 3x3 input window sits in registers and the 32 channels' weights are warp-
+// broadcast from shared memory.  Output: planar [B][32][676] and, for the tensor-core conv2 (TC), also pixel-major
+// [B][676][32] with every value rounded to TF32 (the planar copy carries the same rounded values, so the backward
+// pass differentiates the function the forward pass computed).
+template <bool TC>
 __global__ void __launch_bounds__(256)
 cn_conv1_kernel(const float* __restrict__ params, const uint8_t* __restrict__ images, int64_t n_samples,
-                const int64_t* __restrict__ idx, float* __restrict__ a1) {
+                const int64_t* __restrict__ idx, float* __restrict__ a1, float* __restrict__ a1n) {
     __shared__ float xs[IN];
-    __shared__ float ws[C1 * 9 + C1];
+    __shared__ __align__(16) float ws[9 * C1 + C1];          // [tap][32 channels], then bias[32]
     __shared__ float lut[256];
     const int tid = threadIdx.x, b = blockIdx.x;
     lut[tid] = decode_px(tid);
-    for (int t = tid; t < C1 * 9 + C1; t += 256) ws[t] = params[OFF_C1W + t];     // weights [32][9] then bias [32]
+    for (int t = tid; t < C1 * 9; t += 256) ws[(t % 9) * C1 + t / 9] = params[OFF_C1W + t];     // conv1.weight is [c][tap]
+    if (tid < C1) ws[9 * C1 + tid] = params[OFF_C1B + tid];
     __syncthreads();
     const int64_t s = idx[b];
     const bool ok = s >= 0 && s < n_samples;
@@ -85,15 +44,31 @@ cn_conv1_kernel(const float* __restrict__ params, const uint8_t* __restrict__ im
         xs[t * 4 + 2] = ok ? lut[(v >> 16) & 0xff] : 0.f;  xs[t * 4 + 3] = ok ? lut[v >> 24] : 0.f;
     }
     __syncthreads();
-    float* out = a1 + (size_t)b * C1 * A1;
-    for (int o = tid; o < C1 * A1; o += 256) {
-        const int c = o / A1, pos = o - c * A1, y = pos / H1, x = pos - y * H1;
-        float acc = ws[C1 * 9 + c];
+    float* outp = a1 + (size_t)b * C1 * A1;
+    for (int pos = tid; pos < A1; pos += 256) {
+        const int y = pos / H1, x = pos - y * H1;
+        float win[9];
 #pragma unroll
         for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-            for (int kx = 0; kx < 3; ++kx) acc = fmaf(xs[(y + ky) * 28 + x + kx], ws[c * 9 + ky * 3 + kx], acc);
-        out[o] = fmaxf(acc, 0.f);
+            for (int kx = 0; kx < 3; ++kx) win[ky * 3 + kx] = xs[(y + ky) * 28 + x + kx];
+#pragma unroll 2
+        for (int c4 = 0; c4 < C1; c4 += 4) {
+            float4 acc = *reinterpret_cast<const float4*>(&ws[9 * C1 + c4]);
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const float4 w = *reinterpret_cast<const float4*>(&ws[t * C1 + c4]);
+                acc.x = fmaf(win[t], w.x, acc.x); acc.y = fmaf(win[t], w.y, acc.y);
+                acc.z = fmaf(win[t], w.z, acc.z); acc.w = fmaf(win[t], w.w, acc.w);
+            }
+            acc.x = fmaxf(acc.x, 0.f); acc.y = fmaxf(acc.y, 0.f); acc.z = fmaxf(acc.z, 0.f); acc.w = fmaxf(acc.w, 0.f);
+            if (TC) {
+                acc.x = tf32_round(acc.x); acc.y = tf32_round(acc.y); acc.z = tf32_round(acc.z); acc.w = tf32_round(acc.w);
+                *reinterpret_cast<float4*>(a1n + ((size_t)b * A1 + pos) * C1 + c4) = acc;
+            }
+            outp[(c4 + 0) * A1 + pos] = acc.x; outp[(c4 + 1) * A1 + pos] = acc.y;
+            outp[(c4 + 2) * A1 + pos] = acc.z; outp[(c4 + 3) * A1 + pos] = acc.w;
+        }
     }
 }
 
@@ -688,7 +663,7 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
     const char* who = "ddpm_cn_step_forward";
     DDPM_CHECK_ARG(batch > 0 && batch <= DDPM_CN_MAX_BATCH, "%s: batch %d outside [1, %d]", who, batch, DDPM_CN_MAX_BATCH);
     DDPM_CHECK_ARG(d_params && d_images && d_labels && d_idx && d_workspace && n_samples > 0, "%s: null pointer or empty dataset", who);
-    DDPM_CHECK_ARG((flags & ~(DDPM_FWD_PREP_BACKWARD | DDPM_FWD_PHILOX_MASK)) == 0, "%s: unknown flags %#x", who, flags);
+    DDPM_CHECK_ARG((flags & ~(DDPM_FWD_PREP_BACKWARD | DDPM_FWD_PHILOX_MASK | DDPM_FWD_TF32)) == 0, "%s: unknown flags %#x", who, flags);
     DDPM_CHECK_ARG((d_mask1 == nullptr) == (d_mask2 == nullptr), "%s: give both dropout masks or neither", who);
     DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0 && ((uintptr_t)d_images & 3) == 0, "%s: misaligned pointer", who);
     if (cn_configure()) return 1;
@@ -703,9 +678,19 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
     uint8_t* pflag = (uint8_t*)(ws + L.pflag);
     float* part = (float*)(ws + L.part);
     uint32_t* ctrl = (uint32_t*)(ws + L.ctrl);
-    cn_conv1_kernel<<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1);
-    cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
-                                                                    philox_step, philox ? 1 : 0, train, p2d, pflag);
+    if (flags & DDPM_FWD_TF32) {
+        // conv2 (89 % of the forward flops) as an implicit GEMM on the tensor cores (convnet_tc.cu)
+        float* a1n = (float*)(ws + L.a1n);
+        float* w2t = (float*)(ws + L.w2t);
+        if (launch_cn_w2_prep(d_params, w2t, (float*)(ws + L.w2d), st)) return 1;
+        cn_conv1_kernel<true><<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, a1n);
+        if (launch_cn_conv2_tc(w2t, d_params, a1n, philox ? nullptr : d_mask1, philox_seed, philox_step, philox ? 1 : 0,
+                               train, batch, p2d, pflag, st)) return 1;
+    } else {
+        cn_conv1_kernel<false><<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, nullptr);
+        cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
+                                                                        philox_step, philox ? 1 : 0, train, p2d, pflag);
+    }
     cn_fc1_fwd_kernel<<<KSPLIT, 256, F1_SMEM, st>>>(d_params, p2d, batch, part);
     cn_head_kernel<<<batch, FC, 0, st>>>(d_params, part, d_labels, n_samples, d_idx, philox ? nullptr : d_mask2, philox_seed,
                                          philox_step, philox ? 1 : 0, train, prep, batch, (float*)(ws + L.hd),

@@ -13,7 +13,7 @@
 // proxy fence a single thread issues the chain of tcgen05.mma (M128 N128 K8) into a 128-column TMEM
 // accumulator, commits to an mbarrier, and the warps read their 32 TMEM lanes back with tcgen05.ld
 // and store the split's partial sums, which rows_kernel adds up like any other split-K partial.
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace ddpm {
 
@@ -28,26 +28,9 @@ constexpr size_t TC_SMEM = (size_t)TC_MAX_CHUNKS * 2 * TC_TILE_BYTES + 1024 /*lu
 
 int fc1_tc_ksplit() { return TC_KSPLIT; }
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ float to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
-}
-
-// K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
-//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1)
-//   [32,46) stride byte offset >> 4 (8 rows x 128 B = 1024 B) | [46,48) version = 1 | [61,64) layout = 2
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
 // Instruction descriptor (cute::UMMA::InstrDescriptor) for kind::tf32, FP32 accumulate, both operands
 // K-major: c_format[4,6)=1 (F32), a_format[7,10)=2 (TF32), b_format[10,13)=2, n_dim[17,23)=N>>3, m_dim[24,29)=M>>4
 constexpr uint32_t TC_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(HID >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-
-// byte offset of element (row r, 16-byte chunk q of the 128-byte k row) inside a swizzled tile
-__device__ __forceinline__ uint32_t sw128(int r, int q) { return (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4); }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 fc1_fwd_tc_kernel(const float* __restrict__ W1, const uint8_t* __restrict__ images, int64_t n_samples,

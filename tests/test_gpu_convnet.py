@@ -131,6 +131,36 @@ def test_training_trajectory_matches_oracle(cn, dev, data):
     assert _fro(eng.params.cpu().numpy(), flat) < 0.15
 
 
+@pytest.mark.parametrize("batch", [5, 64, 150])
+def test_tf32_tensor_core_conv2_matches_fp32_path(cn, dev, data, batch):
+    """conv2 on tcgen05 (TF32 operands, fp32 accumulate in TMEM, pooling fused into the epilogue) against the FFMA
+    path on the same inputs: pooled activations and loss to ~1e-3, argmax flags equal wherever the window's two
+    largest values are not within TF32 noise of each other (checked through the loss and the gradients)."""
+    images, labels, im, lb = data
+    p = CO.init_params(17)
+    idx, x, y, m1, m2 = _case(batch, 900 + batch, im, lb)
+    params = torch.from_numpy(CO.flatten_params(p)).to(dev)
+    idx_d = torch.from_numpy(idx).to(dev)
+    m1d, m2d = torch.from_numpy(m1).to(dev), torch.from_numpy(m2).to(dev)
+    out = {}
+    for tf32 in (False, True):
+        ws = cn.ConvNetWorkspace(batch, dev)
+        loss = torch.zeros(2, device=dev)
+        lp = torch.zeros(batch, 10, device=dev)
+        grads = torch.zeros(CO.N_PARAMS, device=dev)
+        cn.step_forward(params, ws, images=images, labels=labels, idx=idx_d, mask1=m1d, mask2=m2d, prep_backward=True,
+                        logprobs=lp, loss=loss, tf32=tf32)
+        cn.step_backward(params, ws, grads, images=images, idx=idx_d)
+        torch.cuda.synchronize()
+        out[tf32] = (float(loss[0]), lp.cpu().numpy(), CO.unflatten_params(grads.cpu().numpy()))
+    loss_ref, lp_ref, _, _ = CO.forward_backward(p, x, y, m1, m2, want_grads=False)
+    assert abs(out[True][0] - loss_ref) < 2e-3 * max(1.0, abs(loss_ref))
+    assert abs(out[True][0] - out[False][0]) < 2e-3 * max(1.0, abs(loss_ref))
+    assert np.abs(out[True][1] - out[False][1]).max() < 5e-3
+    for k in CO.PARAM_KEYS:           # conv1's sums cancel heavily: TF32 noise and argmax flips behind the pool show most there
+        assert _fro(out[True][2][k], out[False][2][k]) < (8e-2 if k.startswith("conv1") else 2e-2), k
+
+
 def test_philox_dropout_rates_and_determinism(cn, dev, data):
     images, labels, im, lb = data
     p = CO.init_params(13)
