@@ -19,8 +19,8 @@
 namespace ddpm {
 
 // ------------------------------------------------------------------------------------------ J1: conv1 + ReLU
-// grid = B, 256 threads.  The 28x28 image is gathered through idx and decoded through the table into shared memory;
-// a thread owns an output pixel: its 3x3 input window sits in registers and the 32 channels' weights are warp-
+// grid = (B, 3), 256 threads.  The 28x28 image is gathered through idx and decoded through the table into shared
+// memory; a thread owns an output pixel: its 3x3 input window sits in registers and the 32 channels' weights are warp-
 // broadcast from shared memory.  Output: planar [B][32][676] and, for the tensor-core conv2 (TC), also pixel-major
 // [B][676][32] with every value rounded to TF32 (the planar copy carries the same rounded values, so the backward
 // pass differentiates the function the forward pass computed).
@@ -45,7 +45,8 @@ cn_conv1_kernel(const float* __restrict__ params, const uint8_t* __restrict__ im
     }
     __syncthreads();
     float* outp = a1 + (size_t)b * C1 * A1;
-    for (int pos = tid; pos < A1; pos += 256) {
+    const int pos = blockIdx.y * 256 + tid;                  // grid.y = 3 covers the 676 pixels
+    if (pos < A1) {
         const int y = pos / H1, x = pos - y * H1;
         float win[9];
 #pragma unroll
@@ -88,12 +89,14 @@ cn_conv2_pool_kernel(const float* __restrict__ params, const float* __restrict__
     float* b2s = w2s + 288 * 32;
     const int tid = threadIdx.x, b = blockIdx.x, half = blockIdx.y;
     const float* src = a1 + (size_t)b * C1 * A1;
+#pragma unroll 8
     for (int t = tid; t < C1 * A1; t += C2_THREADS) {
         const int c = t / A1, pos = t - c * A1;
         a1s[c * A1S + pos] = src[t];
     }
     // conv2.weight is [co][ci][3][3]: element (co, r) with r = ci*9+tap sits at co*288 + r; transposed here to [r][co]
     // (groups of 4 channels XOR-swizzled by r so that this transposing store is 4-way, not 32-way, bank-conflicted)
+#pragma unroll 8
     for (int t = tid; t < 288 * 32; t += C2_THREADS) {
         const int co = t / 288, r = t - co * 288;
         w2s[r * 32 + (((co >> 2) ^ (r & 7)) << 2) + (co & 3)] = params[OFF_C2W + (size_t)(half * 32 + co) * 288 + r];
@@ -165,6 +168,7 @@ cn_fc1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ p2
     float* Ws = sm;                           // [k][n] stride 129
     float* Xs = Ws + 128 * F1_LD;             // [row][k] stride 129
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, ks = blockIdx.x, k0 = ks * 128;
+#pragma unroll 16
     for (int seg = warp; seg < 128 * 4; seg += 8) {          // (unit n, 32 consecutive k): coalesced read, conflict-free write
         const int n = seg >> 2, kk = (seg & 3) * 32 + lane;
         Ws[kk * F1_LD + n] = params[OFF_F1W + (size_t)n * FEAT + k0 + kk];
@@ -172,6 +176,7 @@ cn_fc1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ p2
     const int tn = tid & 15, rg = tid >> 4;
     for (int r0 = 0; r0 < B; r0 += 64) {
         __syncthreads();
+#pragma unroll 16
         for (int seg = warp; seg < 64 * 4; seg += 8) {
             const int r = seg >> 2, kk = (seg & 3) * 32 + lane;
             Xs[r * F1_LD + kk] = (r0 + r < B) ? p2d[(size_t)(r0 + r) * FEAT + k0 + kk] : 0.f;
@@ -219,6 +224,7 @@ cn_head_kernel(const float* __restrict__ params, const float* __restrict__ part,
     __shared__ int last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, b = blockIdx.x;
     float z = 0.f;
+#pragma unroll 24
     for (int ks = 0; ks < KSPLIT; ++ks) z += part[((size_t)ks * B + b) * FC + tid];
     z += params[OFF_F1B + tid];
     const bool pos = z > 0.f;
@@ -289,75 +295,83 @@ cn_head_kernel(const float* __restrict__ params, const float* __restrict__ part,
 }
 
 // ------------------------------------------------------------------------------------------ J4: fc1 backward
-// grid = 72 feature tiles of 128, 256 threads.  CTA kt owns columns [128kt, 128kt+128) of fc1.weight:
+// grid = 144 feature tiles of 64 (one wave on 148 SMs), 256 threads.  CTA kt owns columns [64kt, 64kt+64) of fc1.weight:
 //   dW[n][k] = scale . sum_b dzf[b][n] . p2d[b][k]      (complete: every row of the batch passes through this CTA)
 //   g[b][k]  = sum_n dzf[b][n] . W[n][k], passed through the pooled element's flag (ReLU > 0 and kept) x 1/0.75
-// Rows in chunks of 64; dW accumulates in registers (8 x 8 per thread) across chunks.
-constexpr size_t F1B_SMEM = (size_t)(128 * F1_LD + 64 * 128 + 64 * 128) * 4;
+// Rows in chunks of 64; dW accumulates in registers (8 x 4 per thread) across chunks.
+constexpr int F1B_KT = 64, F1B_LD = F1B_KT + 1;
+constexpr int F1B_TILES = FEAT / F1B_KT;                   // 144
+constexpr size_t F1B_SMEM = (size_t)(128 * F1B_LD + 64 * 128 + 64 * F1B_KT) * 4;
 __global__ void __launch_bounds__(256, 1)
 cn_fc1_bwd_kernel(const float* __restrict__ params, const float* __restrict__ p2d, const uint8_t* __restrict__ pflag,
                   const float* __restrict__ dzf, int B, int train, float scale, float* __restrict__ grads,
                   float* __restrict__ dp2) {
     extern __shared__ __align__(16) float sm[];
-    float* Ws = sm;                           // [n][k] stride 129
-    float* Ds = Ws + 128 * F1_LD;             // [row][n]
+    float* Ws = sm;                           // [n][k] stride 65
+    float* Ds = Ws + 128 * F1B_LD;            // [row][n]
     float* Xs = Ds + 64 * 128;                // [row][k]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, k0 = blockIdx.x * 128;
-    for (int seg = warp; seg < 128 * 4; seg += 8) {
-        const int n = seg >> 2, kk = (seg & 3) * 32 + lane;
-        Ws[n * F1_LD + kk] = params[OFF_F1W + (size_t)n * FEAT + k0 + kk];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, k0 = blockIdx.x * F1B_KT;
+#pragma unroll 16
+    for (int seg = warp; seg < 128 * 2; seg += 8) {          // (unit n, 32 consecutive k)
+        const int n = seg >> 1, kk = (seg & 1) * 32 + lane;
+        Ws[n * F1B_LD + kk] = params[OFF_F1W + (size_t)n * FEAT + k0 + kk];
     }
     const int tk = tid & 15, tn = tid >> 4;                 // dW tile: units tn + 16 i, columns tk + 16 j
-    float dw[8][8];
+    float dw[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+        for (int j = 0; j < 4; ++j) dw[i][j] = 0.f;
     for (int r0 = 0; r0 < B; r0 += 64) {
         __syncthreads();
+#pragma unroll 8
         for (int t = tid; t < 64 * 128; t += 256) {
             const int r = t >> 7, c = t & 127;
-            const bool ok = r0 + r < B;
-            Ds[t] = ok ? dzf[(size_t)(r0 + r) * FC + c] : 0.f;
-            Xs[t] = ok ? p2d[(size_t)(r0 + r) * FEAT + k0 + c] : 0.f;
+            Ds[t] = (r0 + r < B) ? dzf[(size_t)(r0 + r) * FC + c] : 0.f;
+        }
+#pragma unroll 8
+        for (int t = tid; t < 64 * F1B_KT; t += 256) {
+            const int r = t >> 6, c = t & 63;
+            Xs[t] = (r0 + r < B) ? p2d[(size_t)(r0 + r) * FEAT + k0 + c] : 0.f;
         }
         __syncthreads();
+#pragma unroll 4
         for (int r = 0; r < 64; ++r) {
-            float d[8], x[8];
+            float d[8], x[4];
 #pragma unroll
             for (int i = 0; i < 8; ++i) d[i] = Ds[r * 128 + tn + 16 * i];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) x[j] = Xs[r * 128 + tk + 16 * j];
+            for (int j = 0; j < 4; ++j) x[j] = Xs[r * F1B_KT + tk + 16 * j];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) dw[i][j] = fmaf(d[i], x[j], dw[i][j]);
+                for (int j = 0; j < 4; ++j) dw[i][j] = fmaf(d[i], x[j], dw[i][j]);
         }
         // gradient of the pooled activations of these 64 rows: thread -> rows rg*4.., columns tk + 16 j
         const int rg = tid >> 4;
-        float acc[4][8];
+        float acc[4][4];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-#pragma unroll 2
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
         for (int n = 0; n < FC; ++n) {
-            float d[4], w[8];
+            float d[4], w[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) d[i] = Ds[(rg * 4 + i) * 128 + n];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) w[j] = Ws[n * F1_LD + tk + 16 * j];
+            for (int j = 0; j < 4; ++j) w[j] = Ws[n * F1B_LD + tk + 16 * j];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(d[i], w[j], acc[i][j]);
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(d[i], w[j], acc[i][j]);
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int row = r0 + rg * 4 + i;
             if (row < B)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
+                for (int j = 0; j < 4; ++j) {
                     const size_t e = (size_t)row * FEAT + k0 + tk + 16 * j;
                     const bool pass = (pflag[e] & PF_PASS) != 0;
                     dp2[e] = pass ? (train ? acc[i][j] * SCALE1 : acc[i][j]) : 0.f;
@@ -367,7 +381,7 @@ cn_fc1_bwd_kernel(const float* __restrict__ params, const float* __restrict__ p2
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
+        for (int j = 0; j < 4; ++j)
             grads[OFF_F1W + (size_t)(tn + 16 * i) * FEAT + k0 + tk + 16 * j] = dw[i][j] * scale;
 }
 
@@ -400,11 +414,13 @@ cn_conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict_
     for (int hh = 0; hh < 2; ++hh) {
         __syncthreads();
         for (int t = tid; t < 32 * 784; t += DG_THREADS) dzs[t] = 0.f;
+#pragma unroll 8
         for (int t = tid; t < 32 * 9 * 16; t += DG_THREADS) {
             const int ci = t & 15, tap = (t >> 4) % 9, co = t / 144;
             wsm[t] = params[OFF_C2W + ((size_t)(hh * 32 + co) * C1 + half * 16 + ci) * 9 + tap];
         }
         __syncthreads();
+#pragma unroll 4
         for (int t = tid; t < 32 * NPOOL; t += DG_THREADS) {
             const int co = t / NPOOL, p = t - co * NPOOL, py = p / HP, px = p - py * HP;
             const size_t e = (size_t)b * FEAT + (size_t)(hh * 32 + co) * NPOOL + p;
@@ -469,12 +485,14 @@ cn_conv2_wgrad_kernel(const float* __restrict__ a1, const float* __restrict__ dp
     float* dzd = a1s + C1 * A1S;              // [32 co][24*24] dense
     const int tid = threadIdx.x, b = blockIdx.x, half = blockIdx.y;
     const float* src = a1 + (size_t)b * C1 * A1;
+#pragma unroll 8
     for (int t = tid; t < C1 * A1; t += 256) {
         const int c = t / A1, pos = t - c * A1;
         a1s[c * A1S + pos] = src[t];
     }
     for (int t = tid; t < 32 * 576; t += 256) dzd[t] = 0.f;
     __syncthreads();
+#pragma unroll 6
     for (int t = tid; t < 32 * NPOOL; t += 256) {
         const int co = t / NPOOL, p = t - co * NPOOL, py = p / HP, px = p - py * HP;
         const size_t e = (size_t)b * FEAT + (size_t)(half * 32 + co) * NPOOL + p;
@@ -483,10 +501,15 @@ cn_conv2_wgrad_kernel(const float* __restrict__ a1, const float* __restrict__ dp
     }
     __syncthreads();
     float* grow = gpart + (size_t)b * CONV_GRADS;
-    if (tid < 32) {                                          // db2: the 144 pooled gradients of the channel, in order
+    {                                                        // db2: 8 threads per channel, 72 positions each, fixed-order combine
+        const int co = tid >> 3, part = tid & 7;
         float v = 0.f;
-        for (int pos = 0; pos < 576; ++pos) v += dzd[tid * 576 + pos];
-        grow[OFF_C2B + half * 32 + tid] = v;
+#pragma unroll 8
+        for (int i = 0; i < 72; ++i) v += dzd[co * 576 + part * 72 + i];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if (part == 0) grow[OFF_C2B + half * 32 + co] = v;
     }
     const int ci = tid & 31, oct = (tid >> 5) & 3, ph = tid >> 7;
     float acc[8][9];
@@ -546,6 +569,7 @@ cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const
     const int tid = threadIdx.x, b = blockIdx.x;
     if (tid < 256) lut[tid] = decode_px(tid);
     const float* src = dz1 + (size_t)b * C1 * A1;
+#pragma unroll 8
     for (int t = tid; t < C1 * A1; t += 320) {
         const int c = t / A1, pos = t - c * A1;
         dzs[c * A1S + pos] = src[t];
@@ -583,6 +607,7 @@ cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf,
         const int j = blockIdx.x * 256 + tid;
         if (j >= CONV_GRADS) return;
         float v = 0.f;
+#pragma unroll 16
         for (int b = 0; b < B; ++b) v += gpart[(size_t)b * CONV_GRADS + j];
         grads[j] = v * scale;
         return;
@@ -683,11 +708,11 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
         float* a1n = (float*)(ws + L.a1n);
         float* w2t = (float*)(ws + L.w2t);
         if (launch_cn_w2_prep(d_params, w2t, (float*)(ws + L.w2d), st)) return 1;
-        cn_conv1_kernel<true><<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, a1n);
+        cn_conv1_kernel<true><<<dim3(batch, 3), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, a1n);
         if (launch_cn_conv2_tc(w2t, d_params, a1n, philox ? nullptr : d_mask1, philox_seed, philox_step, philox ? 1 : 0,
                                train, batch, p2d, pflag, st)) return 1;
     } else {
-        cn_conv1_kernel<false><<<batch, 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, nullptr);
+        cn_conv1_kernel<false><<<dim3(batch, 3), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, nullptr);
         cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
                                                                         philox_step, philox ? 1 : 0, train, p2d, pflag);
     }
@@ -718,7 +743,7 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
     float* dp2 = (float*)(ws + L.dp2);
     float* dz1 = (float*)(ws + L.dz1);
     float* gpart = (float*)(ws + L.gpart);
-    cn_fc1_bwd_kernel<<<KSPLIT, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
+    cn_fc1_bwd_kernel<<<F1B_TILES, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
     cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
     cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
     cn_conv1_bwd_kernel<<<batch, 320, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);

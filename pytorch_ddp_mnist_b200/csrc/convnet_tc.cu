@@ -88,7 +88,7 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
                 const uint32_t dst = smem_u32(As) + sw128(r, q);
 #pragma unroll
                 for (int tap = 0; tap < 9; ++tap)
-                    cp_async16(dst + (uint32_t)tap * CT_A_TILE, base + ((tap / 3) * H1 + (tap % 3)) * C1, valid ? 16 : 0);
+                    cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base + ((tap / 3) * H1 + (tap % 3)) * C1, valid ? 16 : 0);
             }
         }
         cp_async_wait_all();
@@ -119,6 +119,9 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
             const bool valid = w < nwin;
             const int wv = valid ? w : 0;
             const int b = wv / NPOOL, p = wv - b * NPOOL;
+            // max / argmax over the window's 4 lanes for all 32 channels; lane j keeps channels [8j, 8j+8)
+            float mx[8];
+            int ar[8];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
                 float m = __uint_as_float(v[i]) + bs[c0 + i];
@@ -129,13 +132,18 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
                     const int oa = __shfl_xor_sync(0xffffffffu, arg, off);
                     if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }     // first maximum of the window scan wins
                 }
-                if ((i >> 3) == j && valid) {                                      // the window's 4 lanes share the 32 channels
-                    const size_t e = (size_t)b * FEAT + (size_t)(c0 + i) * NPOOL + p;
+                if ((i >> 3) == j) { mx[i & 7] = m; ar[i & 7] = arg; }
+            }
+            // (kept out of the loop above: there the dropout draw would run, divergently, once per channel per warp)
+            if (valid) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const size_t e = (size_t)b * FEAT + (size_t)(c0 + 8 * j + k) * NPOOL + p;
                     bool keep = true;
                     if (train) keep = use_philox ? philox_keep_thr(seed, step, (uint32_t)e, KEEP1_THR) : (mask1[e] != 0);
-                    const bool pos = m > 0.f;
-                    p2d[e] = (pos && keep) ? (train ? m * SCALE1 : m) : 0.f;
-                    pflag[e] = (uint8_t)((unsigned)arg | ((pos && keep) ? PF_PASS : 0u));
+                    const bool pos = mx[k] > 0.f;
+                    p2d[e] = (pos && keep) ? (train ? mx[k] * SCALE1 : mx[k]) : 0.f;
+                    pflag[e] = (uint8_t)((unsigned)ar[k] | ((pos && keep) ? PF_PASS : 0u));
                 }
             }
         }
