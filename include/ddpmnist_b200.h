@@ -244,8 +244,10 @@ size_t ddpm_cn_workspace_bytes(int max_batch);               /* 0 if max_batch i
 int ddpm_cn_workspace_init(void* d_workspace, int max_batch, void* stream);
 /* Forward (+ loss).  d_mask1 u8[batch][9216] / d_mask2 u8[batch][128]: injected dropout keep masks
  * (both or neither); DDPM_FWD_PHILOX_MASK: masks from Philox4x32-10 at (seed, step); neither: eval
- * mode.  DDPM_FWD_PREP_BACKWARD keeps what ddpm_cn_step_backward needs.  d_logprobs f32[batch][10]
- * or NULL; d_loss f32[2] as in ddpm_step_forward. */
+ * mode.  DDPM_FWD_PREP_BACKWARD keeps what ddpm_cn_step_backward needs.  DDPM_FWD_TF32: conv2 (89 % of
+ * the forward flops) as an implicit GEMM on the tcgen05 tensor cores - TF32 operands, fp32 accumulate,
+ * pooling fused into the TMEM epilogue; ~1e-3 relative.  d_logprobs f32[batch][10] or NULL; d_loss
+ * f32[2] as in ddpm_step_forward. */
 int ddpm_cn_step_forward(const float* d_params,
                          const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
                          const int64_t* d_idx, const uint8_t* d_mask1, const uint8_t* d_mask2,
@@ -253,9 +255,14 @@ int ddpm_cn_step_forward(const float* d_params,
                          float* d_logprobs, float* d_loss, void* d_workspace, void* stream);
 /* Backward of the step whose forward just ran with DDPM_FWD_PREP_BACKWARD on the same workspace:
  * d_grads f32[1199882] = grad_scale x gradient of the mean loss (grad_scale = 1/world_size under
- * data parallelism, then allreduce(SUM) the bucket).  train: the forward's mode (1 = with dropout). */
+ * data parallelism, then allreduce(SUM) the bucket).
+ * flags: DDPM_CN_BWD_TRAIN = the forward ran in training mode (with dropout); DDPM_CN_BWD_TF32 =
+ * conv2's data and weight gradients as implicit GEMMs on the tcgen05 tensor cores (TF32 operands, fp32
+ * accumulate), like DDPM_FWD_TF32 for the forward. */
+#define DDPM_CN_BWD_TRAIN 1u
+#define DDPM_CN_BWD_TF32  2u
 int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_images, int64_t n_samples,
-                          const int64_t* d_idx, int batch, int train, float grad_scale,
+                          const int64_t* d_idx, int batch, unsigned flags, float grad_scale,
                           float* d_grads, void* d_workspace, void* stream);
 /* torch.optim.Adadelta's update on flat arrays (square_avg and acc_delta start at zero); the gradient
  * is multiplied by grad_scale first.  Every operation individually rounded as on the CPU. */

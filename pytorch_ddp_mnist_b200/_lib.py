@@ -17,6 +17,7 @@ IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
 FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
 BWD_TF32 = 1
+CN_BWD_TRAIN, CN_BWD_TF32 = 1, 2
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
 CN_N_PARAMS, CN_MAX_BATCH = 1199882, 8192
@@ -68,7 +69,7 @@ SIGNATURES = {
     "ddpm_cn_workspace_bytes": (C.c_size_t, [_i32]),
     "ddpm_cn_workspace_init": (_i32, [_vp, _i32, _vp]),
     "ddpm_cn_step_forward": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _u64, _u64, _i32, _u32, _vp, _vp, _vp, _vp]),
-    "ddpm_cn_step_backward": (_i32, [_vp, _vp, _i64, _vp, _i32, _i32, _f32, _vp, _vp, _vp]),
+    "ddpm_cn_step_backward": (_i32, [_vp, _vp, _i64, _vp, _i32, _u32, _f32, _vp, _vp, _vp]),
     "ddpm_adadelta_step": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, C.c_double, C.c_double, _f32, _vp]),
     "ddpm_step_backward": (_i32, [_vp, _vp, _i64, _vp, _vp, _vp, _i32, _f32, _f32, _u32, _vp, _vp, _vp]),
     "ddpm_cross_entropy": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp]),

@@ -68,4 +68,7 @@ int launch_cn_w2_prep(const float* params, float* w2t, float* w2d, cudaStream_t 
 int launch_cn_conv2_tc(const float* w2t, const float* params, const float* a1n, const uint8_t* mask1, uint64_t seed,
                        uint64_t step, int use_philox, int train, int B, float* p2d, uint8_t* pflag, cudaStream_t st);
 
+int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* pflag, const float* a1, int B, float* dz2n,
+                             float* dz1, cudaStream_t st);
+
 }  // namespace ddpm

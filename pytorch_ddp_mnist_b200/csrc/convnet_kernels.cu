@@ -726,13 +726,15 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
 }
 
 extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_images, int64_t n_samples,
-                                     const int64_t* d_idx, int batch, int train, float grad_scale, float* d_grads,
+                                     const int64_t* d_idx, int batch, unsigned flags, float grad_scale, float* d_grads,
                                      void* d_workspace, void* stream) {
     const char* who = "ddpm_cn_step_backward";
     DDPM_CHECK_ARG(batch > 0 && batch <= DDPM_CN_MAX_BATCH, "%s: batch %d outside [1, %d]", who, batch, DDPM_CN_MAX_BATCH);
     DDPM_CHECK_ARG(d_params && d_images && d_idx && d_grads && d_workspace && n_samples > 0, "%s: null pointer or empty dataset", who);
     DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0, "%s: misaligned workspace", who);
+    DDPM_CHECK_ARG((flags & ~(DDPM_CN_BWD_TRAIN | DDPM_CN_BWD_TF32)) == 0, "%s: unknown flags %#x", who, flags);
     if (cn_configure()) return 1;
+    const int train = (flags & DDPM_CN_BWD_TRAIN) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
     char* ws = (char*)d_workspace;
     const CnLayout L = cn_layout(batch);
@@ -745,7 +747,13 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
     float* gpart = (float*)(ws + L.gpart);
     cn_fc1_bwd_kernel<<<F1B_TILES, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
     cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
-    cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
+    if (flags & DDPM_CN_BWD_TF32) {
+        float* w2d = (float*)(ws + L.w2d);
+        if (launch_cn_w2_prep(d_params, (float*)(ws + L.w2t), w2d, st)) return 1;
+        if (launch_cn_conv2_dgrad_tc(w2d, dp2, pflag, a1, batch, (float*)(ws + L.dz2n), dz1, st)) return 1;
+    } else {
+        cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
+    }
     cn_conv1_bwd_kernel<<<batch, 320, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
     cn_reduce_kernel<<<RED_BLOCKS + SMALL_BLOCKS, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
                                                                (const float*)(ws + L.hd), batch, grad_scale, d_grads);

@@ -153,6 +153,139 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" :: "r"(tmem_base) : "memory");
 }
 
+// ------------------------------------------------------------------------------------------
+// conv2's data gradient on the tensor cores (row J4):
+//   da1[pos][ci] = sum_{tap, co} dz2pad[pos + (2-ky, 2-kx)][co] . W[co][ci][tap]     M = B.676, N = 32, K = 576
+// dz2 is sparse (one element per pooling window); cn_dz2_build_kernel expands (pooled gradient, argmax flag) into a
+// dense, zero-bordered, pixel-major [B][28x28][64] array, which makes this the same implicit GEMM as the forward
+// pass: per tap two K chunks of 32 output channels (2 x 9 tiles of 128 positions x 128 B, staged in two passes of
+// 144 KB that accumulate into one 32-column TMEM tile), weights as [tap][half][32 ci rows][32 co] tiles.
+// Epilogue: dz1 = da1 . (a1 > 0), written channel-planar for conv1's weight gradient.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+cn_dz2_build_kernel(const float* __restrict__ dp2, const uint8_t* __restrict__ pflag, int B, float* __restrict__ dz2n) {
+    // thread -> (padded pixel, channel); 4 pixels per block of 256
+    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
+    const size_t total = (size_t)B * 784 * C2;
+    if (t >= total) return;
+    const int co = (int)(t & 63);
+    const size_t pix = t >> 6;
+    const int b = (int)(pix / 784), r = (int)(pix - (size_t)b * 784), Y = r / 28, X = r - Y * 28;
+    float v = 0.f;
+    const int y = Y - 2, x = X - 2;
+    if (y >= 0 && y < H2 && x >= 0 && x < H2) {
+        const size_t e = (size_t)b * FEAT + (size_t)co * NPOOL + (y >> 1) * HP + (x >> 1);
+        const unsigned f = pflag[e];
+        if ((f & PF_PASS) && (f & 3u) == (unsigned)(((y & 1) << 1) | (x & 1))) v = to_tf32(dp2[e]);
+    }
+    dz2n[t] = v;
+}
+
+constexpr int DT_W_TILE = 32 * 128;                      // one (tap, half): 32 input channels x 128 B of output channels
+constexpr uint32_t DT_IDESC = umma_idesc_tf32(128, 32);
+constexpr size_t DT_SMEM = (size_t)CT_A_BYTES + 18 * DT_W_TILE + 64 + 1024;
+
+__global__ void __launch_bounds__(CT_THREADS, 1)
+cn_conv2_dgrad_tc_kernel(const float* __restrict__ w2d, const float* __restrict__ dz2n, const float* __restrict__ a1, int B,
+                         float* __restrict__ dz1) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* As = smem;
+    uint8_t* Ws = smem + CT_A_BYTES;                      // [half][tap] tiles of 4 KB
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Ws + 18 * DT_W_TILE);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) mbar_init(mbar, 1);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 32;" :: "r"(smem_u32(tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // weights w2d [tap][ci][64 co]: row (tap, ci) = 256 B = two 128-byte halves -> tile (half, tap), row ci
+    for (int t = tid; t < 9 * C1 * 16; t += CT_THREADS) {
+        const int row = t >> 4, q16 = t & 15, half = q16 >> 3, q = q16 & 7;
+        const int tap = row >> 5, ci = row & 31;
+        cp_async16(smem_u32(Ws) + (uint32_t)(half * 9 + tap) * DT_W_TILE + sw128(ci, q), w2d + (size_t)row * C2 + q16 * 4, 16);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int npos = B * A1;
+    const int ntiles = (npos + 127) / 128;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int half = 0; half < 2; ++half) {
+            const int q = tid & 7;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = (tid >> 3) + 32 * i;
+                const int g = tile * 128 + r;
+                const bool valid = g < npos;
+                const int gv = valid ? g : 0;
+                const int b = gv / A1, pos = gv - b * A1, y = pos / H1, x = pos - y * H1;
+                // tap (ky, kx) reads the padded pixel (y + 2 - ky, x + 2 - kx)
+                const float* base = dz2n + ((size_t)(b * 28 + y + 2) * 28 + x + 2) * C2 + half * 32 + q * 4;
+                const uint32_t dst = smem_u32(As) + sw128(r, q);
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap)
+                    cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base - ((tap / 3) * 28 + (tap % 3)) * C2, valid ? 16 : 0);
+            }
+            cp_async_wait_all();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a0 = smem_u32(As), b0 = smem_u32(Ws) + (uint32_t)half * 9 * DT_W_TILE;
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_tf32(tmem_base, umma_desc_sw128(a0 + tap * CT_A_TILE + k * 32), umma_desc_sw128(b0 + tap * DT_W_TILE + k * 32),
+                                  DT_IDESC, (half | tap | k) ? 1u : 0u);
+                umma_commit(mbar);
+            }
+            mbar_wait(mbar, phase);                         // the tap tiles may be overwritten / the accumulator read
+            phase ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        if (warp < 4) {                                     // 32 columns: one tcgen05.ld per warp covers its 32 positions
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(32 * warp) << 16), v);
+            const int g = tile * 128 + 32 * warp + lane;
+            if (g < npos) {
+                const int b = g / A1, pos = g - b * A1;
+#pragma unroll
+                for (int ci = 0; ci < C1; ++ci) {
+                    const size_t e = ((size_t)b * C1 + ci) * A1 + pos;
+                    dz1[e] = a1[e] > 0.f ? __uint_as_float(v[ci]) : 0.f;
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+    }
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" :: "r"(tmem_base) : "memory");
+}
+
+int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* pflag, const float* a1, int B, float* dz2n,
+                             float* dz1, cudaStream_t st) {
+    static bool configured[64] = {};
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DT_SMEM));
+        configured[dev] = true;
+    }
+    const size_t total = (size_t)B * 784 * C2;
+    cn_dz2_build_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dp2, pflag, B, dz2n);
+    const int ntiles = (B * A1 + 127) / 128;
+    cn_conv2_dgrad_tc_kernel<<<ntiles < 148 ? ntiles : 148, CT_THREADS, DT_SMEM, st>>>(w2d, dz2n, a1, B, dz1);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int launch_cn_w2_prep(const float* params, float* w2t, float* w2d, cudaStream_t st) {
     cn_w2_prep_kernel<<<(C2 * C1 * 9 + 255) / 256, 256, 0, st>>>(params, w2t, w2d);
     DDPM_CUDA(cudaGetLastError());

@@ -150,7 +150,7 @@ def test_tf32_tensor_core_conv2_matches_fp32_path(cn, dev, data, batch):
         grads = torch.zeros(CO.N_PARAMS, device=dev)
         cn.step_forward(params, ws, images=images, labels=labels, idx=idx_d, mask1=m1d, mask2=m2d, prep_backward=True,
                         logprobs=lp, loss=loss, tf32=tf32)
-        cn.step_backward(params, ws, grads, images=images, idx=idx_d)
+        cn.step_backward(params, ws, grads, images=images, idx=idx_d, tf32=tf32)
         torch.cuda.synchronize()
         out[tf32] = (float(loss[0]), lp.cpu().numpy(), CO.unflatten_params(grads.cpu().numpy()))
     loss_ref, lp_ref, _, _ = CO.forward_backward(p, x, y, m1, m2, want_grads=False)
