@@ -23,7 +23,7 @@ constexpr unsigned PF_PASS = 4u;               // bits 0-1: argmax inside the 2x
 
 struct CnLayout {
     size_t ctrl, a1, p2d, pflag, part, hd, dzf, dlog, rowloss, yb, dp2, dz1, gpart;
-    size_t a1n, w2t, w2d, dz2n;               // tensor-core path: a1 as NHWC TF32, conv2.weight as [tap][co][ci] / [tap][half][ci][co], dense padded dz2
+    size_t a1n, w2t, w2d, dz2n, wpart;               // tensor-core path: a1 as NHWC TF32, conv2.weight as [tap][co][ci] / [tap][half][ci][co], dense padded dz2
     size_t total;
 };
 static inline CnLayout cn_layout(int B) {
@@ -47,6 +47,7 @@ static inline CnLayout cn_layout(int B) {
     L.w2t = take((size_t)9 * C2 * C1 * 4);
     L.w2d = take((size_t)9 * C2 * C1 * 4);
     L.dz2n = take((size_t)B * 28 * 28 * C2 * 4);
+    L.wpart = take((size_t)148 * C2 * C1 * 9 * 4);        // per-CTA partial dW2 of the tensor-core weight gradient
     L.total = o;
     return L;
 }
@@ -70,5 +71,8 @@ int launch_cn_conv2_tc(const float* w2t, const float* params, const float* a1n, 
 
 int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* pflag, const float* a1, int B, float* dz2n,
                              float* dz1, cudaStream_t st);
+
+int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
+                             float* wpart, float* grads, cudaStream_t st);
 
 }  // namespace ddpm

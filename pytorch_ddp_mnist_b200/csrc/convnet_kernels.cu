@@ -601,11 +601,11 @@ constexpr int SMALL_N = FC + NC * FC + NC;                 // 1418
 constexpr int SMALL_BLOCKS = (SMALL_N + 255) / 256;        // 6
 __global__ void __launch_bounds__(256)
 cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf, const float* __restrict__ dlog,
-                 const float* __restrict__ hd, int B, float scale, float* __restrict__ grads) {
+                 const float* __restrict__ hd, int B, float scale, int conv1_only, float* __restrict__ grads) {
     const int tid = threadIdx.x;
     if (blockIdx.x < RED_BLOCKS) {
         const int j = blockIdx.x * 256 + tid;
-        if (j >= CONV_GRADS) return;
+        if (j >= (conv1_only ? OFF_C2W : CONV_GRADS)) return;      // conv2's gradients came from the tensor-core kernels
         float v = 0.f;
 #pragma unroll 16
         for (int b = 0; b < B; ++b) v += gpart[(size_t)b * CONV_GRADS + j];
@@ -746,17 +746,21 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
     float* dz1 = (float*)(ws + L.dz1);
     float* gpart = (float*)(ws + L.gpart);
     cn_fc1_bwd_kernel<<<F1B_TILES, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
-    cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
-    if (flags & DDPM_CN_BWD_TF32) {
+    const bool tc = (flags & DDPM_CN_BWD_TF32) != 0;
+    if (tc) {
+        // conv2's data and weight gradients (2/3 of the backward flops) as implicit GEMMs on the tensor cores
         float* w2d = (float*)(ws + L.w2d);
+        float* dz2n = (float*)(ws + L.dz2n);
         if (launch_cn_w2_prep(d_params, (float*)(ws + L.w2t), w2d, st)) return 1;
-        if (launch_cn_conv2_dgrad_tc(w2d, dp2, pflag, a1, batch, (float*)(ws + L.dz2n), dz1, st)) return 1;
+        if (launch_cn_conv2_dgrad_tc(w2d, dp2, pflag, a1, batch, dz2n, dz1, st)) return 1;
+        if (launch_cn_conv2_wgrad_tc(a1, dp2, dz2n, batch, grad_scale, (float*)(ws + L.a1n), (float*)(ws + L.wpart), d_grads, st)) return 1;
     } else {
+        cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
         cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
     }
     cn_conv1_bwd_kernel<<<batch, 320, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
     cn_reduce_kernel<<<RED_BLOCKS + SMALL_BLOCKS, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
-                                                               (const float*)(ws + L.hd), batch, grad_scale, d_grads);
+                                                               (const float*)(ws + L.hd), batch, grad_scale, tc ? 1 : 0, d_grads);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }

@@ -15,6 +15,7 @@
 // (row = 4 . window + dy.2 + dx): the epilogue reads the accumulator with tcgen05.ld, adds the bias, reduces max and
 // argmax over the four lanes with two shuffle rounds, applies ReLU and dropout and writes the pooled activations in
 // fc1's (c, y, x) order plus the flag byte the backward pass needs - conv2's 24x24 output never reaches memory.
+#include <stdlib.h>
 #include "convnet.cuh"
 #include "tc_common.cuh"
 
@@ -282,6 +283,180 @@ int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* 
     cn_dz2_build_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dp2, pflag, B, dz2n);
     const int ntiles = (B * A1 + 127) / 128;
     cn_conv2_dgrad_tc_kernel<<<ntiles < 148 ? ntiles : 148, CT_THREADS, DT_SMEM, st>>>(w2d, dz2n, a1, B, dz1);
+    DDPM_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv2's weight gradient on the tensor cores (row J4):
+//   dW[co][ci][tap] = sum_{b, pos} dz2[b][pos][co] . a1[b][pos + tap][ci]          K = B.576 positions
+// Both operands are pixel-major in memory (the contraction index is the slow one) - for a K-major descriptor they
+// would have to be transposed while staging.  They are not: a tile "row = position, 128 B = 32 channels" is the
+// canonical MN-major layout (for 32-bit operands: SWIZZLE_128B_BASE32B, atom = 4 K-rows x 32 channels with 32-byte
+// granules XOR-ed by the row, next 4 positions at SBO = 512 B, next 32 channels at LBO = the next 16 KB tile), so the
+// same cp.async gather as the forward pass - with that swizzle - feeds the MMA with a_major = b_major = MN.   D[128 x 64] per group: M = 4 taps x 32 ci (4 tap tiles = 4 MN atoms),
+// N = 64 co (the two halves of the 256-byte dz2 rows); three groups cover taps {0-3}, {4-7}, {5-8} (of the last only
+// tap 8's rows are kept), 16 K-steps of 8 positions per 128-position tile, accumulated in TMEM over all tiles of the
+// CTA.  Each CTA writes its partial dW; cn_reduce sums the partials in CTA order.
+// ------------------------------------------------------------------------------------------
+// a1 planar [B][32][676] -> pixel-major TF32 [B][676][32] (makes the backward pass independent of how the forward ran)
+__global__ void __launch_bounds__(256)
+cn_a1n_build_kernel(const float* __restrict__ a1, int B, float* __restrict__ a1n) {
+    __shared__ float t[32][33];
+    const int b = blockIdx.y, p0 = blockIdx.x * 32, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 22 position tiles
+    for (int c = ty; c < 32; c += 8) t[c][tx] = (p0 + tx < A1) ? a1[((size_t)b * C1 + c) * A1 + p0 + tx] : 0.f;
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8)
+        if (p0 + r < A1) a1n[((size_t)b * A1 + p0 + r) * C1 + tx] = to_tf32(t[tx][r]);
+}
+
+// db2[co] = scale . sum of the channel's pooled gradients over the batch (fixed order)
+__global__ void __launch_bounds__(256)
+cn_db2_kernel(const float* __restrict__ dp2, int B, float scale, float* __restrict__ grads) {
+    __shared__ float red[256];
+    const int co = blockIdx.x, tid = threadIdx.x;
+    float v = 0.f;
+    for (int i = tid; i < B * NPOOL; i += 256) {
+        const int b = i / NPOOL, p = i - b * NPOOL;
+        v += dp2[(size_t)b * FEAT + (size_t)co * NPOOL + p];
+    }
+    red[tid] = v;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) red[tid] += red[tid + s];
+        __syncthreads();
+    }
+    if (tid == 0) grads[OFF_C2B + co] = red[0] * scale;
+}
+
+constexpr int WT_B_BYTES = 2 * CT_A_TILE;                // dz2 rows: two channel halves of 128 positions x 128 B
+constexpr size_t WT_SMEM = (size_t)CT_A_BYTES + WT_B_BYTES + 64 + 1024;
+constexpr uint32_t WT_IDESC = umma_idesc_tf32(128, 64) | (1u << 15) | (1u << 16);      // a_major = b_major = MN
+// MN-major descriptor for 32-bit operands: the only layout tcgen05 accepts there is SWIZZLE_128B_BASE32B (layout
+// type 1): atom = 4 K-rows x 128 B, 32-byte granules XOR-ed with the row (Swizzle<2,5,2> on the byte address).
+// LBO = byte distance between 32-channel atoms, SBO = between groups of 4 positions (512 B).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t saddr, uint32_t lbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) | (1ull << 61);
+}
+// byte offset of (position row r, 16-byte piece q of the 128-byte channel row) in such a tile
+__device__ __forceinline__ uint32_t sw128_32b(int r, int q) {
+    return (uint32_t)r * 128u + (uint32_t)((((q >> 1) ^ (r & 3)) << 5) | ((q & 1) << 4));
+}
+
+__global__ void __launch_bounds__(CT_THREADS, 1)
+cn_conv2_wgrad_tc_kernel(const float* __restrict__ a1n, const float* __restrict__ dz2n, int B, float* __restrict__ wpart) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* As = smem;                                   // 9 tap tiles of a1
+    uint8_t* Bs = smem + CT_A_BYTES;                      // 2 channel halves of dz2
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(Bs + WT_B_BYTES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) mbar_init(mbar, 1);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(smem_u32(tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int npos = B * H2 * H2;
+    const int ntiles = (npos + 127) / 128;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        {
+            const int q = tid & 7;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = (tid >> 3) + 32 * i;
+                const int g = tile * 128 + r;
+                const bool valid = g < npos;
+                const int gv = valid ? g : 0;
+                const int b = gv / (H2 * H2), pos = gv - b * (H2 * H2), yo = pos / H2, xo = pos - yo * H2;
+                const float* abase = a1n + ((size_t)(b * H1 + yo) * H1 + xo) * C1 + q * 4;
+                const float* dbase = dz2n + ((size_t)(b * 28 + yo + 2) * 28 + xo + 2) * C2 + q * 4;
+                const uint32_t off = sw128_32b(r, q);
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap)
+                    cp_async16_ca(smem_u32(As) + off + (uint32_t)tap * CT_A_TILE, abase + ((tap / 3) * H1 + (tap % 3)) * C1, valid ? 16 : 0);
+                cp_async16(smem_u32(Bs) + off, dbase, valid ? 16 : 0);
+                cp_async16(smem_u32(Bs) + off + CT_A_TILE, dbase + 32, valid ? 16 : 0);
+            }
+        }
+        cp_async_wait_all();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t a0 = smem_u32(As), b0 = smem_u32(Bs);
+#pragma unroll
+            for (int g = 0; g < 3; ++g) {
+                const uint32_t ag = a0 + (uint32_t)(g == 0 ? 0 : (g == 1 ? 4 : 5)) * CT_A_TILE;
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    umma_tf32(tmem_base + (uint32_t)g * 64, umma_desc_mn_sw128_32b(ag + k * 1024, CT_A_TILE),
+                              umma_desc_mn_sw128_32b(b0 + k * 1024, CT_A_TILE), WT_IDESC, (first && k == 0) ? 0u : 1u);
+            }
+            umma_commit(mbar);
+        }
+        first = false;
+        mbar_wait(mbar, phase);                            // the tiles may be overwritten
+        phase ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    // ---- epilogue: lane = (tap within the group, ci), columns = co; warps 0-3 take co 0..31, warps 4-7 co 32..63
+    {
+        const int w4 = warp & 3, ch = warp >> 2;
+        float* dst = wpart + (size_t)blockIdx.x * (C2 * C1 * 9);
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const int tap = g == 0 ? w4 : (g == 1 ? 4 + w4 : (w4 == 3 ? 8 : -1));
+            if (tap < 0) continue;                          // warp-uniform
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(32 * w4) << 16) + (uint32_t)(g * 64 + ch * 32), v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) dst[((size_t)(ch * 32 + i) * C1 + lane) * 9 + tap] = __uint_as_float(v[i]);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem_base) : "memory");
+}
+
+// sum of the CTAs' partial weight gradients in CTA order
+__global__ void __launch_bounds__(256)
+cn_wpart_reduce_kernel(const float* __restrict__ wpart, int nparts, float scale, float* __restrict__ grads) {
+    const int j = blockIdx.x * 256 + threadIdx.x;
+    if (j >= C2 * C1 * 9) return;
+    float v = 0.f;
+#pragma unroll 8
+    for (int c = 0; c < nparts; ++c) v += wpart[(size_t)c * (C2 * C1 * 9) + j];
+    grads[OFF_C2W + j] = v * scale;
+}
+
+int cn_wgrad_tc_parts(int B) {
+    const int ntiles = (B * H2 * H2 + 127) / 128;
+    return ntiles < 148 ? ntiles : 148;
+}
+
+int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
+                             float* wpart, float* grads, cudaStream_t st) {
+    static bool configured[64] = {};
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WT_SMEM));
+        configured[dev] = true;
+    }
+    const int nparts = cn_wgrad_tc_parts(B);
+    cn_a1n_build_kernel<<<dim3((A1 + 31) / 32, B), 256, 0, st>>>(a1, B, a1n);
+    cn_conv2_wgrad_tc_kernel<<<nparts, CT_THREADS, WT_SMEM, st>>>(a1n, dz2n, B, wpart);
+    cn_wpart_reduce_kernel<<<(C2 * C1 * 9 + 255) / 256, 256, 0, st>>>(wpart, nparts, scale, grads);
+    cn_db2_kernel<<<C2, 256, 0, st>>>(dp2, B, scale, grads);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }
