@@ -261,6 +261,9 @@ int ddpm_cn_step_forward(const float* d_params,
  * accumulate), like DDPM_FWD_TF32 for the forward. */
 #define DDPM_CN_BWD_TRAIN 1u
 #define DDPM_CN_BWD_TF32  2u
+/* with DDPM_CN_BWD_TF32: this step's forward ran with DDPM_FWD_TF32 on the same workspace, so its TF32 copies of
+ * conv2.weight and of conv1's output are reused instead of rebuilt (saves two small kernels) */
+#define DDPM_CN_BWD_FWD_WAS_TF32 4u
 int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_images, int64_t n_samples,
                           const int64_t* d_idx, int batch, unsigned flags, float grad_scale,
                           float* d_grads, void* d_workspace, void* stream);

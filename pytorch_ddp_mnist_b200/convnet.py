@@ -64,15 +64,18 @@ def step_forward(params: torch.Tensor, ws: ConvNetWorkspace, *, images: torch.Te
 
 
 def step_backward(params: torch.Tensor, ws: ConvNetWorkspace, grads: torch.Tensor, *, images: torch.Tensor,
-                  idx: torch.Tensor, train: bool = True, grad_scale: float = 1.0, tf32: bool = False) -> None:
+                  idx: torch.Tensor, train: bool = True, grad_scale: float = 1.0, tf32: bool = False,
+                  forward_was_tf32: bool = False) -> None:
     """Gradient bucket (f32[1199882], scaled by `grad_scale`) of the step whose forward just ran with
-    `prep_backward=True` on `ws`."""
+    `prep_backward=True` on `ws`.  `tf32`: conv2's gradients on the tensor cores; `forward_was_tf32`: that
+    forward also ran with tf32, so its TF32 operand copies in the workspace are reused."""
     _need(params, "params", torch.float32, (CN_N_PARAMS,))
     _need(grads, "grads", torch.float32, (CN_N_PARAMS,))
     _need(images, "images", torch.uint8)
     _need(idx, "idx", torch.int64)
     check(lib.ddpm_cn_step_backward(ptr(params), ptr(images), images.shape[0], ptr(idx), idx.numel(),
-                                    (_lib.CN_BWD_TRAIN if train else 0) | (_lib.CN_BWD_TF32 if tf32 else 0), grad_scale, ptr(grads), ptr(ws.buf), cur_stream()))
+                                    (_lib.CN_BWD_TRAIN if train else 0) | (_lib.CN_BWD_TF32 if tf32 else 0)
+                                    | (_lib.CN_BWD_FWD_WAS_TF32 if (tf32 and forward_was_tf32) else 0), grad_scale, ptr(grads), ptr(ws.buf), cur_stream()))
 
 
 def adadelta_step(params: torch.Tensor, grads: torch.Tensor, square_avg: torch.Tensor, acc_delta: torch.Tensor,
@@ -134,7 +137,7 @@ class ConvNetEngine:
         step_forward(self.params, self.ws, images=resident.images, labels=resident.labels, idx=idx, prep_backward=True,
                      loss=self.loss, tf32=self.tf32, **kw)
         step_backward(self.params, self.ws, self.grads, images=resident.images, idx=idx, train=True,
-                      grad_scale=1.0 / self.world_size, tf32=self.tf32)
+                      grad_scale=1.0 / self.world_size, tf32=self.tf32, forward_was_tf32=self.tf32)
         if self.world_size > 1:
             import torch.distributed as dist
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)

@@ -73,6 +73,6 @@ int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* 
                              float* dz1, cudaStream_t st);
 
 int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
-                             float* wpart, float* grads, cudaStream_t st);
+                             int a1n_ready, float* wpart, float* grads, cudaStream_t st);
 
 }  // namespace ddpm

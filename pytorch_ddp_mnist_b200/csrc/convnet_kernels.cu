@@ -732,7 +732,7 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
     DDPM_CHECK_ARG(batch > 0 && batch <= DDPM_CN_MAX_BATCH, "%s: batch %d outside [1, %d]", who, batch, DDPM_CN_MAX_BATCH);
     DDPM_CHECK_ARG(d_params && d_images && d_idx && d_grads && d_workspace && n_samples > 0, "%s: null pointer or empty dataset", who);
     DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0, "%s: misaligned workspace", who);
-    DDPM_CHECK_ARG((flags & ~(DDPM_CN_BWD_TRAIN | DDPM_CN_BWD_TF32)) == 0, "%s: unknown flags %#x", who, flags);
+    DDPM_CHECK_ARG((flags & ~(DDPM_CN_BWD_TRAIN | DDPM_CN_BWD_TF32 | DDPM_CN_BWD_FWD_WAS_TF32)) == 0, "%s: unknown flags %#x", who, flags);
     if (cn_configure()) return 1;
     const int train = (flags & DDPM_CN_BWD_TRAIN) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
@@ -751,9 +751,11 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
         // conv2's data and weight gradients (2/3 of the backward flops) as implicit GEMMs on the tensor cores
         float* w2d = (float*)(ws + L.w2d);
         float* dz2n = (float*)(ws + L.dz2n);
-        if (launch_cn_w2_prep(d_params, (float*)(ws + L.w2t), w2d, st)) return 1;
+        // DDPM_CN_BWD_FWD_WAS_TF32: the forward left the TF32 weight copies and the pixel-major a1 in this workspace
+        const int ready = (flags & DDPM_CN_BWD_FWD_WAS_TF32) ? 1 : 0;
+        if (!ready && launch_cn_w2_prep(d_params, (float*)(ws + L.w2t), w2d, st)) return 1;
         if (launch_cn_conv2_dgrad_tc(w2d, dp2, pflag, a1, batch, dz2n, dz1, st)) return 1;
-        if (launch_cn_conv2_wgrad_tc(a1, dp2, dz2n, batch, grad_scale, (float*)(ws + L.a1n), (float*)(ws + L.wpart), d_grads, st)) return 1;
+        if (launch_cn_conv2_wgrad_tc(a1, dp2, dz2n, batch, grad_scale, (float*)(ws + L.a1n), ready, (float*)(ws + L.wpart), d_grads, st)) return 1;
     } else {
         cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
         cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);

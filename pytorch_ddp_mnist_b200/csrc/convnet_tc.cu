@@ -165,21 +165,31 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 cn_dz2_build_kernel(const float* __restrict__ dp2, const uint8_t* __restrict__ pflag, int B, float* __restrict__ dz2n) {
-    // thread -> (padded pixel, channel); 4 pixels per block of 256
-    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
-    const size_t total = (size_t)B * 784 * C2;
-    if (t >= total) return;
-    const int co = (int)(t & 63);
-    const size_t pix = t >> 6;
-    const int b = (int)(pix / 784), r = (int)(pix - (size_t)b * 784), Y = r / 28, X = r - Y * 28;
-    float v = 0.f;
-    const int y = Y - 2, x = X - 2;
-    if (y >= 0 && y < H2 && x >= 0 && x < H2) {
-        const size_t e = (size_t)b * FEAT + (size_t)co * NPOOL + (y >> 1) * HP + (x >> 1);
-        const unsigned f = pflag[e];
-        if ((f & PF_PASS) && (f & 3u) == (unsigned)(((y & 1) << 1) | (x & 1))) v = to_tf32(dp2[e]);
+    // one CTA per padded image row (b, Y): the row of pooling windows it overlaps is staged once (64 channels x 12
+    // windows of flags and gradients), then the 28 x 64 outputs are written as one contiguous 7 KB run
+    __shared__ float sg[C2 * HP];
+    __shared__ uint8_t sf[C2 * HP];
+    const int tid = threadIdx.x, b = blockIdx.x / 28, Y = blockIdx.x - b * 28, y = Y - 2;
+    const bool inside = y >= 0 && y < H2;
+    if (inside) {
+        for (int t = tid; t < C2 * HP; t += 256) {
+            const int co = t / HP, px = t - co * HP;
+            const size_t e = (size_t)b * FEAT + (size_t)co * NPOOL + (y >> 1) * HP + px;
+            sf[t] = pflag[e];
+            sg[t] = dp2[e];
+        }
     }
-    dz2n[t] = v;
+    __syncthreads();
+    float* out = dz2n + (size_t)blockIdx.x * 28 * C2;
+    for (int o = tid; o < 28 * C2; o += 256) {
+        const int X = o >> 6, co = o & 63, x = X - 2;
+        float v = 0.f;
+        if (inside && x >= 0 && x < H2) {
+            const unsigned f = sf[co * HP + (x >> 1)];
+            if ((f & PF_PASS) && (f & 3u) == (unsigned)(((y & 1) << 1) | (x & 1))) v = to_tf32(sg[co * HP + (x >> 1)]);
+        }
+        out[o] = v;
+    }
 }
 
 constexpr int DT_W_TILE = 32 * 128;                      // one (tap, half): 32 input channels x 128 B of output channels
@@ -279,8 +289,7 @@ int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* 
         DDPM_CUDA(cudaFuncSetAttribute(cn_conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DT_SMEM));
         configured[dev] = true;
     }
-    const size_t total = (size_t)B * 784 * C2;
-    cn_dz2_build_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(dp2, pflag, B, dz2n);
+    cn_dz2_build_kernel<<<B * 28, 256, 0, st>>>(dp2, pflag, B, dz2n);
     const int ntiles = (B * A1 + 127) / 128;
     cn_conv2_dgrad_tc_kernel<<<ntiles < 148 ? ntiles : 148, CT_THREADS, DT_SMEM, st>>>(w2d, dz2n, a1, B, dz1);
     DDPM_CUDA(cudaGetLastError());
@@ -427,15 +436,19 @@ cn_conv2_wgrad_tc_kernel(const float* __restrict__ a1n, const float* __restrict_
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem_base) : "memory");
 }
 
-// sum of the CTAs' partial weight gradients in CTA order
+// sum of the CTAs' partial weight gradients: four quarter-sums (partials in CTA order) per element, combined in fixed order
 __global__ void __launch_bounds__(256)
 cn_wpart_reduce_kernel(const float* __restrict__ wpart, int nparts, float scale, float* __restrict__ grads) {
-    const int j = blockIdx.x * 256 + threadIdx.x;
-    if (j >= C2 * C1 * 9) return;
+    __shared__ float red[4][64];
+    const int jl = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const int j = blockIdx.x * 64 + jl;                     // 288 blocks x 64 elements
+    const int per = (nparts + 3) / 4, c0 = grp * per, c1 = min(nparts, c0 + per);
     float v = 0.f;
 #pragma unroll 8
-    for (int c = 0; c < nparts; ++c) v += wpart[(size_t)c * (C2 * C1 * 9) + j];
-    grads[OFF_C2W + j] = v * scale;
+    for (int c = c0; c < c1; ++c) v += wpart[(size_t)c * (C2 * C1 * 9) + j];
+    red[grp][jl] = v;
+    __syncthreads();
+    if (grp == 0) grads[OFF_C2W + j] = ((red[0][jl] + red[1][jl]) + (red[2][jl] + red[3][jl])) * scale;
 }
 
 int cn_wgrad_tc_parts(int B) {
@@ -444,7 +457,7 @@ int cn_wgrad_tc_parts(int B) {
 }
 
 int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
-                             float* wpart, float* grads, cudaStream_t st) {
+                             int a1n_ready, float* wpart, float* grads, cudaStream_t st) {
     static bool configured[64] = {};
     int dev = 0;
     DDPM_CUDA(cudaGetDevice(&dev));
@@ -453,9 +466,9 @@ int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2
         configured[dev] = true;
     }
     const int nparts = cn_wgrad_tc_parts(B);
-    cn_a1n_build_kernel<<<dim3((A1 + 31) / 32, B), 256, 0, st>>>(a1, B, a1n);
+    if (!a1n_ready) cn_a1n_build_kernel<<<dim3((A1 + 31) / 32, B), 256, 0, st>>>(a1, B, a1n);
     cn_conv2_wgrad_tc_kernel<<<nparts, CT_THREADS, WT_SMEM, st>>>(a1n, dz2n, B, wpart);
-    cn_wpart_reduce_kernel<<<(C2 * C1 * 9 + 255) / 256, 256, 0, st>>>(wpart, nparts, scale, grads);
+    cn_wpart_reduce_kernel<<<C2 * C1 * 9 / 64, 256, 0, st>>>(wpart, nparts, scale, grads);
     cn_db2_kernel<<<C2, 256, 0, st>>>(dp2, B, scale, grads);
     DDPM_CUDA(cudaGetLastError());
     return 0;

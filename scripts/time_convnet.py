@@ -22,7 +22,7 @@ def timed(fn, n=50):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 fwd = lambda ix: cn.step_forward(eng.params, eng.ws, images=res.images, labels=res.labels, idx=ix, philox=(1, 0), prep_backward=True, loss=eng.loss, tf32=TF32)
-bwd = lambda ix: cn.step_backward(eng.params, eng.ws, eng.grads, images=res.images, idx=ix, tf32=TF32)
+bwd = lambda ix: cn.step_backward(eng.params, eng.ws, eng.grads, images=res.images, idx=ix, tf32=TF32, forward_was_tf32=TF32)
 opt = lambda ix: cn.adadelta_step(eng.params, eng.grads, eng.square_avg, eng.acc_delta)
 step = lambda ix: eng.train_step(res, ix)
 t = {k: timed(f) for k, f in (("forward", fwd), ("backward", bwd), ("adadelta", opt), ("step", step))}
