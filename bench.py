@@ -162,9 +162,28 @@ def main() -> None:
     ap.add_argument("--three-kernel", action="store_true", help="use the v1 three-kernel step instead of the persistent kernel")
     ap.add_argument("--tf32", action="store_true", help="batch > 512 only: fc1 forward and dW1 on tcgen05 TF32 tensor cores (fp32 accumulate)")
     ap.add_argument("--cpu-baseline-steps", type=int, default=150)
+    ap.add_argument("--model", default="ref_mlp", choices=["ref_mlp", "json_convnet"],
+                    help="ref_mlp = the model the reference defines (default, the graded path); json_convnet = the ConvNet "
+                         "BASELINE.json names, which is not in the reference (bench_convnet.py)")
+    ap.add_argument("--fp32", action="store_true", help="json_convnet only: fp32 FFMA kernels instead of tcgen05 TF32")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    if args.model == "json_convnet":
+        import bench_convnet
+        if args.impl == "reference":            # no reference code exists for this model: the CPU arm is the restatement
+            if int(os.environ.get("RANK", "0")) == 0:
+                r = bench_convnet._cpu_baseline(args.batch, 8)
+                print(json.dumps({"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
+                                  "n_gpus": args.gpus, "steps": 8, "warmup": 2, "higher_is_better": True,
+                                  "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                                  "config": {"workload": "json_convnet (not in the reference; CPU restatement)"},
+                                  "cpu_baseline": r, "gpu_launches": 0,
+                                  "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                                          "d2h_bytes_per_step": 0}}), flush=True)
+            return
+        bench_convnet.run(args, ClockSampler, _peaks, METRIC)
+        return
     if args.impl == "reference":
         run_reference_arm(args)
         return

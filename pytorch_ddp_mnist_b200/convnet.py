@@ -22,6 +22,15 @@ PARAM_SHAPES = ((32, 1, 3, 3), (32,), (64, 32, 3, 3), (64,), (128, 9216), (128,)
 FEAT, FC = 9216, 128
 
 
+def init_params_like_torch() -> Dict[str, torch.Tensor]:
+    """torch's default initialisation of the layers BASELINE.json names (current RNG state), under the
+    state_dict keys of the usual `Net` module."""
+    import torch.nn as nn
+    layers = {"conv1": nn.Conv2d(1, 32, 3, 1), "conv2": nn.Conv2d(32, 64, 3, 1), "fc1": nn.Linear(9216, 128),
+              "fc2": nn.Linear(128, 10)}
+    return {f"{n}.{k}": v.detach().clone() for n, m in layers.items() for k, v in m.state_dict().items()}
+
+
 class ConvNetWorkspace:
     """Caller-owned scratch of the ConvNet step (ddpm_cn_workspace_bytes: ~370 KB per image)."""
 
