@@ -173,7 +173,7 @@ def main() -> None:
         import bench_convnet
         if args.impl == "reference":            # no reference code exists for this model: the CPU arm is the restatement
             if int(os.environ.get("RANK", "0")) == 0:
-                r = bench_convnet._cpu_baseline(args.batch, 8)
+                r = bench_convnet._cpu_baseline(args.batch, 150)
                 print(json.dumps({"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
                                   "n_gpus": args.gpus, "steps": 8, "warmup": 2, "higher_is_better": True,
                                   "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

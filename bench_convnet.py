@@ -226,7 +226,7 @@ def run(args, clock_sampler_cls, peaks_fn, metric) -> None:
             "gpu_launches": K * (13 if tf32 else 10), "clocks": clocks, "e2e": e2e, "roofline": roof, "kernels": kernels}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = _cpu_baseline(B, 8)
+            line["cpu_baseline"] = _cpu_baseline(B, 150)
         print(json.dumps(line), flush=True)
     if world > 1:
         sys.stdout.flush()

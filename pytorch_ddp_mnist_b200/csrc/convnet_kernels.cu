@@ -557,40 +557,50 @@ cn_conv2_wgrad_kernel(const float* __restrict__ a1, const float* __restrict__ dp
 }
 
 // conv1's weight gradient of one image: dW1[c][tap] = sum_pos dz1[c][pos] . x[pos + tap], db1[c] = sum_pos dz1[c][pos]
-// (conv1's input needs no gradient).  grid = B, 320 threads: 288 (channel, tap) pairs + 32 bias sums.
-constexpr size_t C1B_SMEM = (size_t)(C1 * A1S + IN + 256) * 4;
-__global__ void __launch_bounds__(320, 1)
+// (conv1's input needs no gradient).  grid = B, 960 threads: (288 (channel, tap) pairs + 32 bias sums) x 3 row
+// groups (rows 0-8, 9-17, 18-25), combined in fixed order through shared memory.
+constexpr int C1B_THREADS = 960;
+constexpr size_t C1B_SMEM = (size_t)(C1 * A1S + IN + 256 + 3 * 320) * 4;
+__global__ void __launch_bounds__(C1B_THREADS, 1)
 cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const int64_t* __restrict__ idx,
                     const float* __restrict__ dz1, float* __restrict__ gpart) {
     extern __shared__ __align__(16) float sm[];
     float* dzs = sm;                          // [32][677]
     float* xs = dzs + C1 * A1S;               // [28*28]
     float* lut = xs + IN;
+    float* red = lut + 256;                   // [3][320]
     const int tid = threadIdx.x, b = blockIdx.x;
     if (tid < 256) lut[tid] = decode_px(tid);
     const float* src = dz1 + (size_t)b * C1 * A1;
 #pragma unroll 8
-    for (int t = tid; t < C1 * A1; t += 320) {
+    for (int t = tid; t < C1 * A1; t += C1B_THREADS) {
         const int c = t / A1, pos = t - c * A1;
         dzs[c * A1S + pos] = src[t];
     }
     __syncthreads();
     const int64_t s = idx[b];
     const bool ok = s >= 0 && s < n_samples;
-    for (int t = tid; t < IN; t += 320) xs[t] = ok ? lut[images[s * IN + t]] : 0.f;
+    for (int t = tid; t < IN; t += C1B_THREADS) xs[t] = ok ? lut[images[s * IN + t]] : 0.f;
     __syncthreads();
-    float* grow = gpart + (size_t)b * CONV_GRADS;
-    if (tid < 288) {
-        const int c = tid / 9, tap = tid - c * 9, ky = tap / 3, kx = tap - ky * 3;
-        float v = 0.f;
-        for (int y = 0; y < H1; ++y)
+    const int part = tid / 320, item = tid - part * 320;       // item < 288: (channel, tap); else bias of channel item - 288
+    const int y0 = part * 9, y1 = min(H1, y0 + 9);
+    float v = 0.f;
+    if (item < 288) {
+        const int c = item / 9, tap = item - c * 9, ky = tap / 3, kx = tap - ky * 3;
+        for (int y = y0; y < y1; ++y)
+#pragma unroll 13
             for (int x = 0; x < H1; ++x) v = fmaf(dzs[c * A1S + y * H1 + x], xs[(y + ky) * 28 + x + kx], v);
-        grow[OFF_C1W + tid] = v;
     } else {
-        const int c = tid - 288;
-        float v = 0.f;
-        for (int pos = 0; pos < A1; ++pos) v += dzs[c * A1S + pos];
-        grow[OFF_C1B + c] = v;
+        const int c = item - 288;
+        for (int pos = y0 * H1; pos < y1 * H1; ++pos) v += dzs[c * A1S + pos];
+    }
+    red[part * 320 + item] = v;
+    __syncthreads();
+    if (tid < 320) {
+        const float sum = (red[tid] + red[320 + tid]) + red[640 + tid];
+        float* grow = gpart + (size_t)b * CONV_GRADS;
+        if (tid < 288) grow[OFF_C1W + tid] = sum;
+        else grow[OFF_C1B + tid - 288] = sum;
     }
 }
 
@@ -760,7 +770,7 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
         cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
         cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
     }
-    cn_conv1_bwd_kernel<<<batch, 320, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
+    cn_conv1_bwd_kernel<<<batch, C1B_THREADS, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
     cn_reduce_kernel<<<RED_BLOCKS + SMALL_BLOCKS, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
                                                                (const float*)(ws + L.hd), batch, grad_scale, tc ? 1 : 0, d_grads);
     DDPM_CUDA(cudaGetLastError());
