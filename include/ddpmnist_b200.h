@@ -174,7 +174,8 @@ void ddpm_comm_destroy(ddpm_comm* c);
  *   d_idx      i64[nsteps*batch]: this rank's batches (may be NULL when d_idx_all is given)
  *   d_idx_all  i64[world][idx_stride], row r = rank r's batches of this launch (DistributedSampler shards are a
  *              pure function of (seed, epoch, rank), so every rank can compute all of them), or NULL.
- *              When given and batch <= 64, fc1's gradient (85 % of the bucket) is not exchanged at all: ranks
+ *              When given, batch <= 64 and world <= 4 (beyond that the extra multiply work outweighs the saved
+ *              traffic), fc1's gradient (85 % of the bucket) is not exchanged at all: ranks
  *              exchange their dz1 rows (32 KB) and each forms the global-batch dW1 tile itself from the
  *              resident dataset — same sums in the same (rank) order on every rank. */
 int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,

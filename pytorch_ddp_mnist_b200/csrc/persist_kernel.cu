@@ -1128,7 +1128,10 @@ extern "C" int ddpm_train_steps_fused_ddp(
     memset(&a, 0, sizeof(a));
     comm_fill(a, comm);
     // fc1's gradient through the dz1 exchange when every rank's indices are known and the batch is one chunk
-    a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
+    // (measured, batch 64: ws 2: 9.96 -> 11.0 M img/s, ws 4: 14.8 -> 15.7 M, ws 8: 23.9 -> 19.9 M - every rank then
+    //  multiplies ws x 64 rows of pixels per tile, which outweighs the saved traffic beyond 4 ranks; DDPM_ACT_EXCHANGE=1 forces it)
+    const bool act_default = comm->world <= 4 || getenv("DDPM_ACT_EXCHANGE") != nullptr;
+    a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && act_default && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
     if (a.act_exchange && getenv("DDPM_ACT_EXCHANGE_ALL") != nullptr) a.act_exchange = 2;   // also W2 / W3 / biases (measured slower at ws = 2)
     a.idx_all = d_idx_all; a.idx_stride = (size_t)idx_stride;
     if (d_idx == nullptr && d_idx_all != nullptr) d_idx = d_idx_all + (size_t)comm->rank * idx_stride;
