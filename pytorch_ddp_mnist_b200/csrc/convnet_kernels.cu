@@ -626,14 +626,17 @@ cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf,
     if (e >= SMALL_N) return;
     float v = 0.f;
     if (e < FC) {
+#pragma unroll 16
         for (int b = 0; b < B; ++b) v += dzf[(size_t)b * FC + e];
         grads[OFF_F1B + e] = v * scale;
     } else if (e < FC + NC * FC) {
         const int c = (e - FC) / FC, n = (e - FC) - c * FC;
+#pragma unroll 16
         for (int b = 0; b < B; ++b) v = fmaf(dlog[(size_t)b * NCP + c], hd[(size_t)b * FC + n], v);
         grads[OFF_F2W + c * FC + n] = v * scale;
     } else {
         const int c = e - FC - NC * FC;
+#pragma unroll 16
         for (int b = 0; b < B; ++b) v += dlog[(size_t)b * NCP + c];
         grads[OFF_F2B + c] = v * scale;
     }
@@ -644,18 +647,31 @@ cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf,
 //   sq <- rho sq + (1-rho) g g ; std = sqrt(sq + eps) ; delta = sqrt(acc + eps) / std . g ;
 //   acc <- rho acc + (1-rho) delta delta ; p <- p - lr delta
 // Every operation individually rounded (no contraction), as the CPU's vectorised elementwise kernels do.
+__device__ __forceinline__ void adadelta_elem(float& p, float g, float& sq, float& acc, float lr, float rho,
+                                              float one_minus_rho, float eps, float gscale) {
+    const float gv = __fmul_rn(g, gscale);
+    const float s = __fadd_rn(__fmul_rn(sq, rho), __fmul_rn(__fmul_rn(one_minus_rho, gv), gv));
+    const float std = __fsqrt_rn(__fadd_rn(s, eps));
+    const float delta = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(acc, eps)), std), gv);
+    acc = __fadd_rn(__fmul_rn(acc, rho), __fmul_rn(__fmul_rn(one_minus_rho, delta), delta));
+    sq = s;
+    p = fmaf(-lr, delta, p);
+}
 __global__ void __launch_bounds__(256)
 adadelta_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, float* __restrict__ acc,
-                int64_t n, float lr, float rho, float one_minus_rho, float eps, float gscale) {
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
-        const float gv = __fmul_rn(g[i], gscale);
-        const float s = __fadd_rn(__fmul_rn(sq[i], rho), __fmul_rn(__fmul_rn(one_minus_rho, gv), gv));
-        const float std = __fsqrt_rn(__fadd_rn(s, eps));
-        const float delta = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(acc[i], eps)), std), gv);
-        const float a = __fadd_rn(__fmul_rn(acc[i], rho), __fmul_rn(__fmul_rn(one_minus_rho, delta), delta));
-        sq[i] = s; acc[i] = a;
-        p[i] = fmaf(-lr, delta, p[i]);
+                int64_t n, float lr, float rho, float one_minus_rho, float eps, float gscale, int vec) {
+    const int64_t n4 = vec ? n / 4 : 0;                       // 16-byte path when all four arrays are 16-byte aligned
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+        float4 pv = reinterpret_cast<float4*>(p)[i], sv = reinterpret_cast<float4*>(sq)[i], av = reinterpret_cast<float4*>(acc)[i];
+        const float4 gv = reinterpret_cast<const float4*>(g)[i];
+        adadelta_elem(pv.x, gv.x, sv.x, av.x, lr, rho, one_minus_rho, eps, gscale);
+        adadelta_elem(pv.y, gv.y, sv.y, av.y, lr, rho, one_minus_rho, eps, gscale);
+        adadelta_elem(pv.z, gv.z, sv.z, av.z, lr, rho, one_minus_rho, eps, gscale);
+        adadelta_elem(pv.w, gv.w, sv.w, av.w, lr, rho, one_minus_rho, eps, gscale);
+        reinterpret_cast<float4*>(p)[i] = pv; reinterpret_cast<float4*>(sq)[i] = sv; reinterpret_cast<float4*>(acc)[i] = av;
     }
+    for (int64_t i = n4 * 4 + (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+        adadelta_elem(p[i], g[i], sq[i], acc[i], lr, rho, one_minus_rho, eps, gscale);
 }
 
 }  // namespace ddpm
@@ -781,9 +797,11 @@ extern "C" int ddpm_adadelta_step(float* d_params, const float* d_grads, float* 
                                   int64_t n, float lr, double rho, double eps, float grad_scale, void* stream) {
     DDPM_CHECK_ARG(d_params && d_grads && d_square_avg && d_acc_delta && n > 0, "ddpm_adadelta_step: null pointer or n <= 0");
     const float one_minus_rho = (float)(1.0 - rho);          // torch forms 1 - rho in double, then rounds once
-    const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+    const int vec = ((((uintptr_t)d_params | (uintptr_t)d_grads | (uintptr_t)d_square_avg | (uintptr_t)d_acc_delta) & 15) == 0) ? 1 : 0;
+    const int64_t work = vec ? (n + 3) / 4 : n;
+    const int blocks = (int)((work + 255) / 256 < 148 * 8 ? (work + 255) / 256 : 148 * 8);
     adadelta_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_params, d_grads, d_square_avg, d_acc_delta, n, lr, (float)rho,
-                                                              one_minus_rho, (float)eps, grad_scale);
+                                                              one_minus_rho, (float)eps, grad_scale, vec);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }

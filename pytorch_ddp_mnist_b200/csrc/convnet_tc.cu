@@ -73,25 +73,26 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
     const int nwin = B * NPOOL;
     const int ntiles = (nwin + 31) / 32;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        // ---- gather the 9 tap tiles: 8 consecutive threads copy one 128-byte pixel row
-        {
-            const int q = tid & 7;
+    // gather of the 9 tap tiles of one position tile: 8 consecutive threads copy one 128-byte pixel row
+    auto gather = [&](int tile) {
+        const int q = tid & 7;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = (tid >> 3) + 32 * i;
-                const int w = tile * 32 + (r >> 2), j = r & 3;
-                const bool valid = w < nwin;
-                const int wv = valid ? w : 0;
-                const int b = wv / NPOOL, p = wv - b * NPOOL, py = p / HP, px = p - py * HP;
-                const int yo = 2 * py + (j >> 1), xo = 2 * px + (j & 1);
-                const float* base = a1n + ((size_t)(b * H1 + yo) * H1 + xo) * C1 + q * 4;
-                const uint32_t dst = smem_u32(As) + sw128(r, q);
+        for (int i = 0; i < 4; ++i) {
+            const int r = (tid >> 3) + 32 * i;
+            const int w = tile * 32 + (r >> 2), j = r & 3;
+            const bool valid = w < nwin;
+            const int wv = valid ? w : 0;
+            const int b = wv / NPOOL, p = wv - b * NPOOL, py = p / HP, px = p - py * HP;
+            const int yo = 2 * py + (j >> 1), xo = 2 * px + (j & 1);
+            const float* base = a1n + ((size_t)(b * H1 + yo) * H1 + xo) * C1 + q * 4;
+            const uint32_t dst = smem_u32(As) + sw128(r, q);
 #pragma unroll
-                for (int tap = 0; tap < 9; ++tap)
-                    cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base + ((tap / 3) * H1 + (tap % 3)) * C1, valid ? 16 : 0);
-            }
+            for (int tap = 0; tap < 9; ++tap)
+                cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base + ((tap / 3) * H1 + (tap % 3)) * C1, valid ? 16 : 0);
         }
+    };
+    if ((int)blockIdx.x < ntiles) gather(blockIdx.x);
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         cp_async_wait_all();
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> async proxy (tcgen05.mma)
         __syncthreads();
@@ -109,6 +110,8 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
         mbar_wait(mbar, phase);
         phase ^= 1;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // the MMAs have consumed the tap tiles: the next tile's gather flies while this one's epilogue runs
+        if (tile + (int)gridDim.x < ntiles) gather(tile + gridDim.x);
 
         // ---- epilogue: warp -> TMEM lanes 32.(warp & 3).., columns 32.(warp >> 2)..; lane = position within the tile
         {
@@ -226,23 +229,26 @@ cn_conv2_dgrad_tc_kernel(const float* __restrict__ w2d, const float* __restrict_
     const int npos = B * A1;
     const int ntiles = (npos + 127) / 128;
     uint32_t phase = 0;
+    auto gather = [&](int tile, int half) {
+        const int q = tid & 7;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = (tid >> 3) + 32 * i;
+            const int g = tile * 128 + r;
+            const bool valid = g < npos;
+            const int gv = valid ? g : 0;
+            const int b = gv / A1, pos = gv - b * A1, y = pos / H1, x = pos - y * H1;
+            // tap (ky, kx) reads the padded pixel (y + 2 - ky, x + 2 - kx)
+            const float* base = dz2n + ((size_t)(b * 28 + y + 2) * 28 + x + 2) * C2 + half * 32 + q * 4;
+            const uint32_t dst = smem_u32(As) + sw128(r, q);
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap)
+                cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base - ((tap / 3) * 28 + (tap % 3)) * C2, valid ? 16 : 0);
+        }
+    };
+    if ((int)blockIdx.x < ntiles) gather(blockIdx.x, 0);
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int half = 0; half < 2; ++half) {
-            const int q = tid & 7;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = (tid >> 3) + 32 * i;
-                const int g = tile * 128 + r;
-                const bool valid = g < npos;
-                const int gv = valid ? g : 0;
-                const int b = gv / A1, pos = gv - b * A1, y = pos / H1, x = pos - y * H1;
-                // tap (ky, kx) reads the padded pixel (y + 2 - ky, x + 2 - kx)
-                const float* base = dz2n + ((size_t)(b * 28 + y + 2) * 28 + x + 2) * C2 + half * 32 + q * 4;
-                const uint32_t dst = smem_u32(As) + sw128(r, q);
-#pragma unroll
-                for (int tap = 0; tap < 9; ++tap)
-                    cp_async16_ca(dst + (uint32_t)tap * CT_A_TILE, base - ((tap / 3) * 28 + (tap % 3)) * C2, valid ? 16 : 0);
-            }
             cp_async_wait_all();
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
@@ -260,6 +266,9 @@ cn_conv2_dgrad_tc_kernel(const float* __restrict__ w2d, const float* __restrict_
             mbar_wait(mbar, phase);                         // the tap tiles may be overwritten / the accumulator read
             phase ^= 1;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // next operand pass: the other channel half, or the next tile's first half (overlaps the epilogue below)
+            if (half == 0) gather(tile, 1);
+            else if (tile + (int)gridDim.x < ntiles) gather(tile + gridDim.x, 0);
         }
         if (warp < 4) {                                     // 32 columns: one tcgen05.ld per warp covers its 32 positions
             uint32_t v[32];
