@@ -279,6 +279,8 @@ __device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long
         for (int r = 0; r < a.world; ++r)
             if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
     }
+    // (polling every source at once before summing was tried: the extra live registers spill in the 255-register
+    //  kernel and the step got slower at 2 and 4 GPUs: 10.97 -> 8.94 M, 15.7 -> 13.3 M img/s)
     float sum[N];
     for (int r = 0; r < a.world; ++r) {
         float got[N];
@@ -353,7 +355,9 @@ __device__ __forceinline__ void act_stage(const PersistArgs& a, unsigned long lo
     }
 }
 
-template <bool FEED>                                  // FEED: host-fed mode (batches arrive in a device ring while the kernel runs)
+// FEED: host-fed mode (batches arrive in a device ring while the kernel runs); DDP: world > 1 (in-kernel gradient
+// exchange) - a template parameter so that the single-GPU kernel carries none of the exchange code or its registers
+template <bool FEED, bool DDP>
 __global__ void __launch_bounds__(P_THREADS, 1)
 train_persist_kernel(PersistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -402,7 +406,7 @@ train_persist_kernel(PersistArgs a) {
         const uint8_t* mask = a.masks ? a.masks + (size_t)step * B * HID : nullptr;
         float* xs_cur = s.xs[step & 1];
         const bool prefetch = own_w1 && single && (step + 1 < a.nsteps);
-        const bool ddp = a.world > 1;
+        constexpr bool ddp = DDP;
         const bool actx = ddp && a.act_exchange && single;           // W1 through the dz1 exchange
         const bool actx_all = actx && a.act_exchange == 2;           // ... and W2 / W3 / biases through dz2, h1d, h2, dz3
         const unsigned long long T = a.comm_step + step + 1;            // global step number of this communicator
@@ -961,7 +965,8 @@ static int persist_configure() {
     if (dev >= 0 && dev < 64 && !configured[dev]) {
         int sms = 0;
         DDPM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        const void* fns[2] = {(const void*)train_persist_kernel<false>, (const void*)train_persist_kernel<true>};
+        const void* fns[4] = {(const void*)train_persist_kernel<false, false>, (const void*)train_persist_kernel<true, false>,
+                              (const void*)train_persist_kernel<false, true>, (const void*)train_persist_kernel<true, true>};
         for (const void* fn : fns) {
             int per_sm = 0;
             DDPM_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1006,7 +1011,9 @@ static int persist_fill_and_launch(PersistArgs& a, float* d_params, float* d_gra
     a.bar = (unsigned long long*)(ws + L.ctrl) + 2;     // ctrl words 4..7
     a.dbg = g_persist_dbg;
     void* kargs[] = {&a};
-    const void* fn = a.feed_flags ? (const void*)train_persist_kernel<true> : (const void*)train_persist_kernel<false>;
+    const bool feed = a.feed_flags != nullptr, ddp = a.world > 1;
+    const void* fn = feed ? (ddp ? (const void*)train_persist_kernel<true, true> : (const void*)train_persist_kernel<true, false>)
+                          : (ddp ? (const void*)train_persist_kernel<false, true> : (const void*)train_persist_kernel<false, false>);
     DDPM_CUDA(cudaLaunchCooperativeKernel(fn, dim3(P_GRID), dim3(P_THREADS), kargs, sizeof(PersistSmem), (cudaStream_t)stream));
     return 0;
 }
