@@ -126,6 +126,33 @@ def main():
     dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "host-fed fused replicas diverged"
     dist.barrier()
+    # ---- BASELINE.json's ConvNet (not in the reference; oracle = restatement): bucket all-reduce over NCCL.
+    # Each rank's gradient of its own 16-sample batch, pre-divided by ws and summed, must equal the gradient of the
+    # mean loss over the global batch (the restatement evaluated on all ws x 16 samples), and replicas must agree.
+    from oracle import convnet_oracle as CO
+    from pytorch_ddp_mnist_b200 import convnet as cn
+    cb = 16
+    crng = np.random.default_rng(4242)
+    cidx = crng.integers(0, 60000, (world, cb)).astype(np.int64)
+    cm1 = (crng.random((world, cb, 9216)) < 0.75).astype(np.uint8)
+    cm2 = (crng.random((world, cb, 128)) < 0.5).astype(np.uint8)
+    cp = CO.init_params(5)
+    ceng = cn.ConvNetEngine(dev, cb, world_size=world, rank=rank)
+    ceng.load_state_dict(cp)
+    ceng.train_step(res, torch.from_numpy(cidx[rank]).to(dev), torch.from_numpy(cm1[rank]).to(dev),
+                    torch.from_numpy(cm2[rank]).to(dev))
+    torch.cuda.synchronize()
+    xs, ys = O.gather_decode(im, lb, cidx.reshape(-1))
+    _, _, cg, _ = CO.forward_backward(cp, xs.reshape(world * cb, 784), ys, cm1.reshape(world * cb, 9216),
+                                      cm2.reshape(world * cb, 128))
+    gref = CO.flatten_params(cg).astype(np.float64)
+    cerr = float(np.linalg.norm(ceng.grads.cpu().numpy() - gref) / np.linalg.norm(gref))
+    assert cerr < 1e-4, ("convnet all-reduced gradient vs global-batch restatement", cerr)
+    mine = ceng.params.clone()
+    other = mine.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(mine, other), "convnet replicas diverged"
+    dist.barrier()
     if rank == 0:
         print("MULTIGPU_OK world %d exchange %s act_exchange %s max loss err %.2e fused-vs-nccl %.2e" %
               (world, os.environ.get("DDPM_EXCHANGE", "default"), "off" if os.environ.get("DDPM_NO_ACT_EXCHANGE") else "on",
