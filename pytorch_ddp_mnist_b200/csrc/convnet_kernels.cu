@@ -742,7 +742,11 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
         cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
                                                                         philox_step, philox ? 1 : 0, train, p2d, pflag);
     }
-    cn_fc1_fwd_kernel<<<KSPLIT, 256, F1_SMEM, st>>>(d_params, p2d, batch, part);
+    if (flags & DDPM_FWD_TF32) {
+        if (launch_cn_fc1_fwd_tc(d_params, p2d, batch, part, st)) return 1;
+    } else {
+        cn_fc1_fwd_kernel<<<KSPLIT, 256, F1_SMEM, st>>>(d_params, p2d, batch, part);
+    }
     cn_head_kernel<<<batch, FC, 0, st>>>(d_params, part, d_labels, n_samples, d_idx, philox ? nullptr : d_mask2, philox_seed,
                                          philox_step, philox ? 1 : 0, train, prep, batch, (float*)(ws + L.hd),
                                          (float*)(ws + L.dzf), (float*)(ws + L.dlog), d_logprobs, (float*)(ws + L.rowloss),
@@ -771,8 +775,12 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
     float* dp2 = (float*)(ws + L.dp2);
     float* dz1 = (float*)(ws + L.dz1);
     float* gpart = (float*)(ws + L.gpart);
-    cn_fc1_bwd_kernel<<<F1B_TILES, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
     const bool tc = (flags & DDPM_CN_BWD_TF32) != 0;
+    if (tc) {
+        if (launch_cn_fc1_bwd_tc(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2, st)) return 1;
+    } else {
+        cn_fc1_bwd_kernel<<<F1B_TILES, 256, F1B_SMEM, st>>>(d_params, p2d, pflag, dzf, batch, train ? 1 : 0, grad_scale, d_grads, dp2);
+    }
     if (tc) {
         // conv2's data and weight gradients (2/3 of the backward flops) as implicit GEMMs on the tensor cores
         float* w2d = (float*)(ws + L.w2d);
