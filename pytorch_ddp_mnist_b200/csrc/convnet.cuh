@@ -58,6 +58,20 @@ __host__ __device__ inline bool philox_keep_thr(uint64_t seed, uint64_t step, ui
     return r[elem & 3] < thr;
 }
 
+// Dropout(.25) draws for 8 consecutive channels [co0, co0+8) (co0 % 8 == 0) of pooled position p of image b: the
+// random stream is indexed channel-fastest, (b.144 + p).64 + co, so the 8 draws are two Philox blocks of four
+// 32-bit words - a draw per element indexed in fc1's (c, y, x) order would cost a whole block per element.
+__host__ __device__ inline unsigned philox_keep8(uint64_t seed, uint64_t step, int b, int p, int co0, uint32_t thr) {
+    const uint32_t blk = ((uint32_t)(b * NPOOL + p) * C2 + (uint32_t)co0) >> 2;
+    uint32_t r0[4], r1[4];
+    Philox::gen(seed, step, blk, r0);
+    Philox::gen(seed, step, blk + 1, r1);
+    unsigned m = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m |= (r0[i] < thr ? 1u : 0u) << i | (r1[i] < thr ? 1u : 0u) << (4 + i);
+    return m;
+}
+
 __device__ __forceinline__ float tf32_round(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));

@@ -136,6 +136,7 @@ cn_conv2_pool_kernel(const float* __restrict__ params, const float* __restrict__
                                 acc[dy * 2 + dx][j] = fmaf(patch[dy + ky][dx + kx], w[j], acc[dy * 2 + dx][j]);
                 }
         }
+        const unsigned keep8 = (train && use_philox) ? philox_keep8(seed, step, b, p, half * 32 + co0, KEEP1_THR) : 0xffu;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int co = half * 32 + co0 + j;
@@ -149,7 +150,7 @@ cn_conv2_pool_kernel(const float* __restrict__ params, const float* __restrict__
             }
             const size_t e = (size_t)b * FEAT + (size_t)co * NPOOL + p;
             bool keep = true;
-            if (train) keep = use_philox ? philox_keep_thr(seed, step, (uint32_t)e, KEEP1_THR) : (mask1[e] != 0);
+            if (train) keep = use_philox ? ((keep8 >> j) & 1u) != 0 : (mask1[e] != 0);
             const bool pos = m > 0.f;
             p2d[e] = (pos && keep) ? (train ? m * SCALE1 : m) : 0.f;
             pflag[e] = (uint8_t)(arg | ((pos && keep) ? PF_PASS : 0u));

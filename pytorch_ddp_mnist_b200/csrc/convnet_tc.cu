@@ -140,11 +140,12 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
             }
             // (kept out of the loop above: there the dropout draw would run, divergently, once per channel per warp)
             if (valid) {
+                const unsigned keep8 = (train && use_philox) ? philox_keep8(seed, step, b, p, c0 + 8 * j, KEEP1_THR) : 0xffu;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const size_t e = (size_t)b * FEAT + (size_t)(c0 + 8 * j + k) * NPOOL + p;
                     bool keep = true;
-                    if (train) keep = use_philox ? philox_keep_thr(seed, step, (uint32_t)e, KEEP1_THR) : (mask1[e] != 0);
+                    if (train) keep = use_philox ? ((keep8 >> k) & 1u) != 0 : (mask1[e] != 0);
                     const bool pos = mx[k] > 0.f;
                     p2d[e] = (pos && keep) ? to_tf32(train ? mx[k] * SCALE1 : mx[k]) : 0.f;    // fc1's TF32 operand
                     pflag[e] = (uint8_t)((unsigned)ar[k] | ((pos && keep) ? PF_PASS : 0u));

@@ -161,6 +161,29 @@ def test_tf32_tensor_core_conv2_matches_fp32_path(cn, dev, data, batch):
         assert _fro(out[True][2][k], out[False][2][k]) < (8e-2 if k.startswith("conv1") else 2e-2), k
 
 
+def test_philox_mask_is_the_same_in_both_paths(cn, dev, data):
+    """The in-kernel Philox dropout draw is indexed (image, pooled position, channel) in the FFMA kernel and in the
+    tcgen05 epilogue alike: with the same (seed, step) both paths must see the same masks, i.e. their losses agree
+    to TF32 accuracy (different masks would move the loss by several per cent)."""
+    images, labels, im, lb = data
+    p = CO.init_params(19)
+    params = torch.from_numpy(CO.flatten_params(p)).to(dev)
+    idx = torch.arange(100, 164, dtype=torch.int64, device=dev)
+    losses = []
+    for tf32 in (False, True):
+        ws = cn.ConvNetWorkspace(64, dev)
+        loss = torch.zeros(2, device=dev)
+        cn.step_forward(params, ws, images=images, labels=labels, idx=idx, philox=(77, 3), loss=loss, tf32=tf32)
+        torch.cuda.synchronize()
+        losses.append(float(loss[0]))
+    assert abs(losses[0] - losses[1]) < 3e-3 * abs(losses[0]), losses
+    ws = cn.ConvNetWorkspace(64, dev)
+    loss = torch.zeros(2, device=dev)
+    cn.step_forward(params, ws, images=images, labels=labels, idx=idx, loss=loss)          # eval mode: no dropout
+    torch.cuda.synchronize()
+    assert abs(float(loss[0]) - losses[0]) > 1e-3 * abs(losses[0])                       # the masks did something
+
+
 def test_philox_dropout_rates_and_determinism(cn, dev, data):
     images, labels, im, lb = data
     p = CO.init_params(13)
