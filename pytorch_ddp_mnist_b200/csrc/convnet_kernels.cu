@@ -562,7 +562,7 @@ cn_conv2_wgrad_kernel(const float* __restrict__ a1, const float* __restrict__ dp
 // groups (rows 0-8, 9-17, 18-25), combined in fixed order through shared memory.
 constexpr int C1B_THREADS = 960;
 constexpr size_t C1B_SMEM = (size_t)(C1 * A1S + IN + 256 + 3 * 320) * 4;
-__global__ void __launch_bounds__(C1B_THREADS, 1)
+__global__ void __launch_bounds__(C1B_THREADS, 2)
 cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const int64_t* __restrict__ idx,
                     const float* __restrict__ dz1, float* __restrict__ gpart) {
     extern __shared__ __align__(16) float sm[];
@@ -605,42 +605,37 @@ cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const
     }
 }
 
-// sum of the per-image partial gradients (fixed image order) and the three small gradients of the dense layers
-// (fc1.bias, fc2.weight, fc2.bias: sums over the batch of dzf, dlogits x hd, dlogits).
-constexpr int RED_BLOCKS = (CONV_GRADS + 255) / 256;       // 74
+// sum of the per-image partial gradients and the three small gradients of the dense layers (fc1.bias, fc2.weight,
+// fc2.bias: sums over the batch of dzf, dlogits x hd, dlogits).  One warp per output element: lane l takes images
+// l, l+32, ... (in order), then the 32 lane sums are combined by a fixed shuffle tree - the same order every run.
 constexpr int SMALL_N = FC + NC * FC + NC;                 // 1418
-constexpr int SMALL_BLOCKS = (SMALL_N + 255) / 256;        // 6
 __global__ void __launch_bounds__(256)
 cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf, const float* __restrict__ dlog,
-                 const float* __restrict__ hd, int B, float scale, int conv1_only, float* __restrict__ grads) {
-    const int tid = threadIdx.x;
-    if (blockIdx.x < RED_BLOCKS) {
-        const int j = blockIdx.x * 256 + tid;
-        if (j >= (conv1_only ? OFF_C2W : CONV_GRADS)) return;      // conv2's gradients came from the tensor-core kernels
-        float v = 0.f;
-#pragma unroll 16
-        for (int b = 0; b < B; ++b) v += gpart[(size_t)b * CONV_GRADS + j];
-        grads[j] = v * scale;
-        return;
-    }
-    const int e = (blockIdx.x - RED_BLOCKS) * 256 + tid;
-    if (e >= SMALL_N) return;
+                 const float* __restrict__ hd, int B, float scale, int nconv, float* __restrict__ grads) {
+    const int lane = threadIdx.x & 31;
+    const int e = blockIdx.x * 8 + (threadIdx.x >> 5);     // 8 elements per block
+    if (e >= nconv + SMALL_N) return;
     float v = 0.f;
-    if (e < FC) {
-#pragma unroll 16
-        for (int b = 0; b < B; ++b) v += dzf[(size_t)b * FC + e];
-        grads[OFF_F1B + e] = v * scale;
-    } else if (e < FC + NC * FC) {
-        const int c = (e - FC) / FC, n = (e - FC) - c * FC;
-#pragma unroll 16
-        for (int b = 0; b < B; ++b) v = fmaf(dlog[(size_t)b * NCP + c], hd[(size_t)b * FC + n], v);
-        grads[OFF_F2W + c * FC + n] = v * scale;
+    int out;
+    if (e < nconv) {                                       // conv1 (+ conv2 in the FFMA path): per-image partials
+        for (int b = lane; b < B; b += 32) v += gpart[(size_t)b * CONV_GRADS + e];
+        out = e;
+    } else if (e < nconv + FC) {
+        const int n = e - nconv;
+        for (int b = lane; b < B; b += 32) v += dzf[(size_t)b * FC + n];
+        out = OFF_F1B + n;
+    } else if (e < nconv + FC + NC * FC) {
+        const int c = (e - nconv - FC) / FC, n = (e - nconv - FC) - c * FC;
+        for (int b = lane; b < B; b += 32) v = fmaf(dlog[(size_t)b * NCP + c], hd[(size_t)b * FC + n], v);
+        out = OFF_F2W + c * FC + n;
     } else {
-        const int c = e - FC - NC * FC;
-#pragma unroll 16
-        for (int b = 0; b < B; ++b) v += dlog[(size_t)b * NCP + c];
-        grads[OFF_F2B + c] = v * scale;
+        const int c = e - nconv - FC - NC * FC;
+        for (int b = lane; b < B; b += 32) v += dlog[(size_t)b * NCP + c];
+        out = OFF_F2B + c;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) grads[out] = v * scale;
 }
 
 // ------------------------------------------------------------------------------------------ J5: Adadelta
@@ -796,8 +791,9 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
         cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
     }
     cn_conv1_bwd_kernel<<<batch, C1B_THREADS, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
-    cn_reduce_kernel<<<RED_BLOCKS + SMALL_BLOCKS, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
-                                                               (const float*)(ws + L.hd), batch, grad_scale, tc ? 1 : 0, d_grads);
+    const int nconv = tc ? OFF_C2W : CONV_GRADS;            // conv2's gradients came from the tensor-core kernels
+    cn_reduce_kernel<<<(nconv + SMALL_N + 7) / 8, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
+                                                              (const float*)(ws + L.hd), batch, grad_scale, nconv, d_grads);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }

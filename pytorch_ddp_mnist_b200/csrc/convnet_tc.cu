@@ -335,6 +335,7 @@ cn_db2_kernel(const float* __restrict__ dp2, int B, float scale, float* __restri
     __shared__ float red[256];
     const int co = blockIdx.x, tid = threadIdx.x;
     float v = 0.f;
+#pragma unroll 8
     for (int i = tid; i < B * NPOOL; i += 256) {
         const int b = i / NPOOL, p = i - b * NPOOL;
         v += dp2[(size_t)b * FEAT + (size_t)co * NPOOL + p];
