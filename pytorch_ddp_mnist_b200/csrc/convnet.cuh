@@ -72,6 +72,16 @@ __host__ __device__ inline unsigned philox_keep8(uint64_t seed, uint64_t step, i
     return m;
 }
 
+// the same stream for 4 consecutive channels [co0, co0+4), co0 % 4 == 0: one block
+__host__ __device__ inline unsigned philox_keep4(uint64_t seed, uint64_t step, int b, int p, int co0, uint32_t thr) {
+    uint32_t r0[4];
+    Philox::gen(seed, step, ((uint32_t)(b * NPOOL + p) * C2 + (uint32_t)co0) >> 2, r0);
+    unsigned m = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m |= (r0[i] < thr ? 1u : 0u) << i;
+    return m;
+}
+
 __device__ __forceinline__ float tf32_round(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));

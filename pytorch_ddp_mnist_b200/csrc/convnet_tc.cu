@@ -41,7 +41,8 @@ cn_w2_prep_kernel(const float* __restrict__ params, float* __restrict__ w2t, flo
     w2d[(tap * C1 + ci) * C2 + co] = v;
 }
 
-__global__ void __launch_bounds__(CT_THREADS, 1)
+constexpr int C2T_THREADS = 512;      // 16 warps: the kernel is issue-latency bound (ncu: one instruction per ~7 cycles per warp)
+__global__ void __launch_bounds__(C2T_THREADS, 1)
 cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ params, const float* __restrict__ a1n,
                    const uint8_t* __restrict__ mask1, uint64_t seed, uint64_t step, int use_philox, int train, int B,
                    float* __restrict__ p2d, uint8_t* __restrict__ pflag) {
@@ -61,7 +62,7 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
     }
     if (tid < C2) bs[tid] = params[OFF_C2B + tid];
     // weights: 9 x 64 rows of 128 B, 8 chunks each
-    for (int t = tid; t < 9 * C2 * 8; t += CT_THREADS) {
+    for (int t = tid; t < 9 * C2 * 8; t += C2T_THREADS) {
         const int row = t >> 3, q = t & 7;
         cp_async16(smem_u32(Ws) + (uint32_t)(row >> 6) * CT_W_TILE + sw128(row & 63, q), w2t + (size_t)row * C1 + q * 4, 16);
     }
@@ -77,8 +78,8 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
     auto gather = [&](int tile) {
         const int q = tid & 7;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int r = (tid >> 3) + 32 * i;
+        for (int i = 0; i < 2; ++i) {
+            const int r = (tid >> 3) + 64 * i;
             const int w = tile * 32 + (r >> 2), j = r & 3;
             const bool valid = w < nwin;
             const int wv = valid ? w : 0;
@@ -113,21 +114,21 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
         // the MMAs have consumed the tap tiles: the next tile's gather flies while this one's epilogue runs
         if (tile + (int)gridDim.x < ntiles) gather(tile + gridDim.x);
 
-        // ---- epilogue: warp -> TMEM lanes 32.(warp & 3).., columns 32.(warp >> 2)..; lane = position within the tile
+        // ---- epilogue: warp -> TMEM lanes 32.(warp & 3).., columns 16.(warp >> 2)..; lane = position within the tile
         {
-            uint32_t v[32];
-            const int lrow = 32 * (warp & 3) + lane, c0 = 32 * (warp >> 2);
-            tmem_ld_32x32(tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)c0, v);
+            uint32_t v[16];
+            const int lrow = 32 * (warp & 3) + lane, c0 = 16 * (warp >> 2);
+            tmem_ld_32x16(tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)c0, v);
             const int j = lane & 3;
             const int w = tile * 32 + (lrow >> 2);
             const bool valid = w < nwin;
             const int wv = valid ? w : 0;
             const int b = wv / NPOOL, p = wv - b * NPOOL;
-            // max / argmax over the window's 4 lanes for all 32 channels; lane j keeps channels [8j, 8j+8)
-            float mx[8];
-            int ar[8];
+            // max / argmax over the window's 4 lanes for the warp's 16 channels; lane j keeps channels [4j, 4j+4)
+            float mx[4];
+            int ar[4];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
+            for (int i = 0; i < 16; ++i) {
                 float m = __uint_as_float(v[i]) + bs[c0 + i];
                 int arg = j;
 #pragma unroll
@@ -136,16 +137,16 @@ cn_conv2_tc_kernel(const float* __restrict__ w2t, const float* __restrict__ para
                     const int oa = __shfl_xor_sync(0xffffffffu, arg, off);
                     if (om > m || (om == m && oa < arg)) { m = om; arg = oa; }     // first maximum of the window scan wins
                 }
-                if ((i >> 3) == j) { mx[i & 7] = m; ar[i & 7] = arg; }
+                if ((i >> 2) == j) { mx[i & 3] = m; ar[i & 3] = arg; }
             }
             // (kept out of the loop above: there the dropout draw would run, divergently, once per channel per warp)
             if (valid) {
-                const unsigned keep8 = (train && use_philox) ? philox_keep8(seed, step, b, p, c0 + 8 * j, KEEP1_THR) : 0xffu;
+                const unsigned keep4 = (train && use_philox) ? philox_keep4(seed, step, b, p, c0 + 4 * j, KEEP1_THR) : 0xfu;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const size_t e = (size_t)b * FEAT + (size_t)(c0 + 8 * j + k) * NPOOL + p;
+                for (int k = 0; k < 4; ++k) {
+                    const size_t e = (size_t)b * FEAT + (size_t)(c0 + 4 * j + k) * NPOOL + p;
                     bool keep = true;
-                    if (train) keep = use_philox ? ((keep8 >> k) & 1u) != 0 : (mask1[e] != 0);
+                    if (train) keep = use_philox ? ((keep4 >> k) & 1u) != 0 : (mask1[e] != 0);
                     const bool pos = mx[k] > 0.f;
                     p2d[e] = (pos && keep) ? to_tf32(train ? mx[k] * SCALE1 : mx[k]) : 0.f;    // fc1's TF32 operand
                     pflag[e] = (uint8_t)((unsigned)ar[k] | ((pos && keep) ? PF_PASS : 0u));
@@ -733,7 +734,7 @@ int launch_cn_conv2_tc(const float* w2t, const float* params, const float* a1n, 
     }
     const int ntiles = (B * NPOOL + 31) / 32;
     const int grid = ntiles < 148 ? ntiles : 148;
-    cn_conv2_tc_kernel<<<grid, CT_THREADS, CT_SMEM, st>>>(w2t, params, a1n, mask1, seed, step, use_philox, train, B, p2d, pflag);
+    cn_conv2_tc_kernel<<<grid, C2T_THREADS, CT_SMEM, st>>>(w2t, params, a1n, mask1, seed, step, use_philox, train, B, p2d, pflag);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }
