@@ -9,11 +9,12 @@
  * Conventions
  *   - plain C types only; every pointer named d_* is a DEVICE pointer owned by the caller
  *     (PyTorch tensors in practice), h_* is a HOST pointer.  The library allocates no device
- *     memory and keeps no pointer after a call returns (one exception: the ddpm_comm_* communicator
- *     of the fused data-parallel step owns one small symmetric buffer).
+ *     memory and keeps no pointer after a call returns (two exceptions, both explicit objects the
+ *     caller creates and destroys: the ddpm_comm_* communicator of the fused data-parallel step owns
+ *     one small symmetric buffer, a ddpm_feed_* host feed owns its ring of batch slots).
  *   - every GPU entry point is asynchronous and ordered on `stream` (a cudaStream_t passed as
- *     void*; NULL = legacy default stream); none of them synchronises or allocates, so they can be
- *     captured in a CUDA graph.
+ *     void*; NULL = legacy default stream); none of them synchronises or allocates (the host-fed loop
+ *     additionally uses the feed's own copy streams).
  *   - return value: 0 = ok, non-zero = error; ddpm_last_error() returns a thread-local message.
  *   - flat parameter layout (118,272 fp32 = 473,088 B, the reference's single DDP bucket), in
  *     `model.parameters()` order, each matrix row-major [out,in] (mp:412-422):
@@ -135,7 +136,7 @@ int ddpm_step_backward(float* d_params,
  *   d_loss       f32[2] as in ddpm_step_forward (may be NULL); d_loss_steps f32[nsteps] per-step
  *                mean loss (may be NULL)
  * batch must be <= 512 (larger batches are compute-bound: use the step_forward/backward pair).
- * The device must be able to co-schedule the kernel's 123 blocks (any B200 does). */
+ * The device must be able to co-schedule the kernel's 148 blocks, one per SM (any B200 does). */
 int ddpm_train_steps_persistent(float* d_params, float* d_grads,
                                 const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
                                 const int64_t* d_idx, const uint8_t* d_masks,
