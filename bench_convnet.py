@@ -98,7 +98,7 @@ def run(args, clock_sampler_cls, peaks_fn, metric) -> None:
     sampler = DistributedSampler(_IndexOnly(N), num_replicas=world, rank=rank, shuffle=True, seed=42)
     sampler.set_epoch(0)
     shard = torch.tensor(list(iter(sampler)), dtype=torch.int64)
-    need = (W + K) * B
+    need = (W + K + 110) * B                                # + the per-phase timing section's 100 fresh batches
     shard_dev = shard.repeat(-(-need // shard.numel()))[:need].to(dev)
     eng = cn.ConvNetEngine(dev, B, world_size=world, rank=rank, tf32=tf32)
     torch.manual_seed(0)

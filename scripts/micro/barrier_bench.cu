@@ -64,6 +64,26 @@ __global__ void __launch_bounds__(256, 1) k(unsigned long long* ctr, float* buf,
             if (tid < gridDim.x) { while (ld_relaxed(ctr + 16 * (tid + 1)) < target) { } }
             asm volatile("fence.acq_rel.gpu;" ::: "memory");
             __syncthreads();
+        } else if (MODE == 6 || MODE == 7) {                               // 2 / 4 counters (CTA index mod), arrive on one, poll all
+            constexpr int NC = MODE == 6 ? 2 : 4;
+            __syncthreads();
+            if (tid == 255) {
+                target += 1;                                               // every counter reaches (#CTAs mapped to it) x target
+                asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(ctr + 16 * (blockIdx.x % NC)) : "memory");
+                bool done = false;
+                while (!done) {
+                    unsigned long long v[NC];
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) v[c] = ld_acquire(ctr + 16 * c);
+                    done = true;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const unsigned long long members = (gridDim.x - c + NC - 1) / NC;
+                        done = done && (v[c] >= members * target);
+                    }
+                }
+            }
+            __syncthreads();
         }
     }
     if (blockIdx.x == 0 && tid == 0) out[0] = (clock64() - t0) / iters;
@@ -89,5 +109,7 @@ int main() {
     run<3>("__threadfence + atomicAdd + volatile poll + __threadfence", ctr, buf, out);
     run<4>("relaxed red + relaxed poll, no fences (lower bound)", ctr, buf, out);
     run<5>("per-CTA release flags, 148 threads poll one flag each", ctr, buf, out);
+    run<6>("red.release on 2 counters (CTA parity), acquire-poll both", ctr, buf, out);
+    run<7>("red.release on 4 counters, acquire-poll all four", ctr, buf, out);
     return 0;
 }
