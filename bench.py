@@ -232,8 +232,9 @@ def main() -> None:
     eng.broadcast_params()
 
     # ---- ws == 1: the persistent kernel runs CHUNK whole steps per launch straight off the shard.
-    # ---- ws  > 1: CUDA graph of CHUNK unrolled steps (persistent 1-step kernel -> NCCL allreduce ->
-    #      flat SGD) reading a fixed index buffer that is refilled per replay.
+    # ---- ws  > 1: the same, with the gradient exchange inside the kernel (fused, default); --no-fused: CUDA graph
+    #      of CHUNK unrolled steps (persistent 1-step kernel -> NCCL allreduce -> flat SGD) reading a fixed index
+    #      buffer that is refilled per replay.  Batches > 512 / --three-kernel: CUDA graph of the v1 kernels.
     chunk = min(CHUNK, K)
     persistent = (B <= 512) and not args.three_kernel
     idx_buf = torch.empty(chunk * B, dtype=torch.int64, device=dev)
