@@ -156,5 +156,15 @@ class ConvNetEngine:
         step_forward(self.params, self.ws, images=resident.images, labels=resident.labels, idx=idx, loss=self.loss,
                      logprobs=logprobs)
 
+    def scale_lr(self, gamma: float) -> None:
+        """`StepLR(step_size=1, gamma)` of the recipe BASELINE.json describes: call once per epoch."""
+        self.lr *= float(gamma)
+
+    def accuracy(self, resident, idx: torch.Tensor) -> float:
+        """Fraction of the samples `idx` whose arg-max class equals the label (eval mode; the test loop's metric)."""
+        lp = torch.empty(idx.numel(), 10, dtype=torch.float32, device=self.device)
+        self.eval_step(resident, idx, logprobs=lp)
+        return float((lp.argmax(dim=1) == resident.labels[idx].to(torch.int64)).float().mean().item())
+
     def last_batch_loss(self) -> float:
         return float(self.loss[0].item())

@@ -217,3 +217,27 @@ def test_argument_errors(cn, dev, data):
         cn.step_forward(params, ws, images=images, labels=labels, idx=torch.arange(9, dtype=torch.int64, device=dev))
     with pytest.raises(ValueError):
         cn.ConvNetWorkspace(10 ** 6, dev)
+
+
+@pytest.mark.parametrize("tf32", [False, True])
+def test_training_reduces_loss_and_fits_a_batch(cn, dev, data, tf32):
+    """End to end: 40 Adadelta steps (Philox dropout on) on one fixed batch of 64 - forward, backward and optimizer
+    together must fit it: loss falls below a third of its start and the batch is classified > 90 % right."""
+    images, labels, im, lb = data
+    from pytorch_ddp_mnist_b200.dataset import ResidentDataset
+    res = ResidentDataset.from_arrays(im, lb, dev)
+    torch.manual_seed(3)
+    eng = cn.ConvNetEngine(dev, 64, tf32=tf32)
+    eng.load_state_dict(cn.init_params_like_torch())
+    idx = torch.arange(500, 564, dtype=torch.int64, device=dev)
+    eng.eval_step(res, idx)
+    first = eng.last_batch_loss()
+    acc0 = eng.accuracy(res, idx)
+    for _ in range(40):
+        eng.train_step(res, idx)
+    eng.eval_step(res, idx)
+    last = eng.last_batch_loss()
+    assert np.isfinite(last) and last < first / 3, (first, last)
+    assert eng.accuracy(res, idx) > 0.9 > acc0
+    eng.scale_lr(0.7)
+    assert abs(eng.lr - 0.7) < 1e-12
