@@ -353,17 +353,6 @@ cn_db2_kernel(const float* __restrict__ dp2, int B, float scale, float* __restri
 constexpr int WT_B_BYTES = 2 * CT_A_TILE;                // dz2 rows: two channel halves of 128 positions x 128 B
 constexpr size_t WT_SMEM = (size_t)CT_A_BYTES + WT_B_BYTES + 64 + 1024;
 constexpr uint32_t WT_IDESC = umma_idesc_tf32(128, 64) | (1u << 15) | (1u << 16);      // a_major = b_major = MN
-// MN-major descriptor for 32-bit operands: the only layout tcgen05 accepts there is SWIZZLE_128B_BASE32B (layout
-// type 1): atom = 4 K-rows x 128 B, 32-byte granules XOR-ed with the row (Swizzle<2,5,2> on the byte address).
-// LBO = byte distance between 32-channel atoms, SBO = between groups of 4 positions (512 B).
-__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t saddr, uint32_t lbo_bytes) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) | (1ull << 61);
-}
-// byte offset of (position row r, 16-byte piece q of the 128-byte channel row) in such a tile
-__device__ __forceinline__ uint32_t sw128_32b(int r, int q) {
-    return (uint32_t)r * 128u + (uint32_t)((((q >> 1) ^ (r & 3)) << 5) | ((q & 1) << 4));
-}
-
 __global__ void __launch_bounds__(CT_THREADS, 1)
 cn_conv2_wgrad_tc_kernel(const float* __restrict__ a1n, const float* __restrict__ dz2n, int B, float* __restrict__ wpart) {
     extern __shared__ uint8_t smem_raw[];

@@ -48,6 +48,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* mbar, uint32_t parity) {
                      "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smem_u32(mbar)), "r"(parity) : "memory");
     }
 }
+// MN-major descriptor for 32-bit operands: the only layout tcgen05 accepts there is SWIZZLE_128B_BASE32B (layout
+// type 1): atom = 4 K-rows x 128 B, 32-byte granules XOR-ed with the row (Swizzle<2,5,2> on the byte address).
+// LBO = byte distance between 32-channel atoms, SBO = between groups of 4 positions (512 B).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t saddr, uint32_t lbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) | (1ull << 46) | (1ull << 61);
+}
+// byte offset of (position row r, 16-byte piece q of the 128-byte channel row) in such a tile
+__device__ __forceinline__ uint32_t sw128_32b(int r, int q) {
+    return (uint32_t)r * 128u + (uint32_t)((((q >> 1) ^ (r & 3)) << 5) | ((q & 1) << 4));
+}
+
 // 32 consecutive fp32 columns of this warp's 32 TMEM lanes (thread = lane)
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
