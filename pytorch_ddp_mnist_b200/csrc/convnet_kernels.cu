@@ -27,7 +27,19 @@ namespace ddpm {
 template <bool TC>
 __global__ void __launch_bounds__(256)
 cn_conv1_kernel(const float* __restrict__ params, const uint8_t* __restrict__ images, int64_t n_samples,
-                const int64_t* __restrict__ idx, float* __restrict__ a1, float* __restrict__ a1n) {
+                const int64_t* __restrict__ idx, float* __restrict__ a1, float* __restrict__ a1n,
+                float* __restrict__ w2t, float* __restrict__ w2d) {
+    if (TC && blockIdx.y == 3) {
+        // fourth layer of CTAs (tensor-core mode): conv2.weight [co][ci][tap] -> TF32 copies w2t [tap][co][ci] (forward,
+        // K = ci) and w2d [tap][ci][co] (data gradient, K = co) - same launch, one dependent kernel less
+        for (int t = blockIdx.x * 256 + threadIdx.x; t < C2 * C1 * 9; t += gridDim.x * 256) {
+            const int co = t / (C1 * 9), r = t - co * (C1 * 9), ci = r / 9, tap = r - ci * 9;
+            const float v = tf32_round(params[OFF_C2W + t]);
+            w2t[(tap * C2 + co) * C1 + ci] = v;
+            w2d[(tap * C1 + ci) * C2 + co] = v;
+        }
+        return;
+    }
     __shared__ float xs[IN];
     __shared__ __align__(16) float ws[9 * C1 + C1];          // [tap][32 channels], then bias[32]
     __shared__ float lut[256];
@@ -729,12 +741,11 @@ extern "C" int ddpm_cn_step_forward(const float* d_params, const uint8_t* d_imag
         // conv2 (89 % of the forward flops) as an implicit GEMM on the tensor cores (convnet_tc.cu)
         float* a1n = (float*)(ws + L.a1n);
         float* w2t = (float*)(ws + L.w2t);
-        if (launch_cn_w2_prep(d_params, w2t, (float*)(ws + L.w2d), st)) return 1;
-        cn_conv1_kernel<true><<<dim3(batch, 3), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, a1n);
+        cn_conv1_kernel<true><<<dim3(batch, 4), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, a1n, w2t, (float*)(ws + L.w2d));
         if (launch_cn_conv2_tc(w2t, d_params, a1n, philox ? nullptr : d_mask1, philox_seed, philox_step, philox ? 1 : 0,
                                train, batch, p2d, pflag, st)) return 1;
     } else {
-        cn_conv1_kernel<false><<<dim3(batch, 3), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, nullptr);
+        cn_conv1_kernel<false><<<dim3(batch, 3), 256, 0, st>>>(d_params, d_images, n_samples, d_idx, a1, nullptr, nullptr, nullptr);
         cn_conv2_pool_kernel<<<dim3(batch, 2), C2_THREADS, C2_SMEM, st>>>(d_params, a1, philox ? nullptr : d_mask1, philox_seed,
                                                                         philox_step, philox ? 1 : 0, train, p2d, pflag);
     }

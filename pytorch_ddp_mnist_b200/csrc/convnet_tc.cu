@@ -331,10 +331,9 @@ cn_a1n_build_kernel(const float* __restrict__ a1, int B, float* __restrict__ a1n
 }
 
 // db2[co] = scale . sum of the channel's pooled gradients over the batch (fixed order)
-__global__ void __launch_bounds__(256)
-cn_db2_kernel(const float* __restrict__ dp2, int B, float scale, float* __restrict__ grads) {
+__device__ __forceinline__ void db2_block(const float* __restrict__ dp2, int B, float scale, float* __restrict__ grads, int co) {
     __shared__ float red[256];
-    const int co = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     float v = 0.f;
 #pragma unroll 8
     for (int i = tid; i < B * NPOOL; i += 256) {
@@ -439,7 +438,12 @@ cn_conv2_wgrad_tc_kernel(const float* __restrict__ a1n, const float* __restrict_
 
 // sum of the CTAs' partial weight gradients: four quarter-sums (partials in CTA order) per element, combined in fixed order
 __global__ void __launch_bounds__(256)
-cn_wpart_reduce_kernel(const float* __restrict__ wpart, int nparts, float scale, float* __restrict__ grads) {
+cn_wpart_reduce_kernel(const float* __restrict__ wpart, int nparts, const float* __restrict__ dp2, int B, float scale,
+                       float* __restrict__ grads) {
+    if (blockIdx.x >= C2 * C1 * 9 / 64) {                  // the last 64 blocks: conv2.bias (same launch, one dependency less)
+        db2_block(dp2, B, scale, grads, blockIdx.x - C2 * C1 * 9 / 64);
+        return;
+    }
     __shared__ float red[4][64];
     const int jl = threadIdx.x & 63, grp = threadIdx.x >> 6;
     const int j = blockIdx.x * 64 + jl;                     // 288 blocks x 64 elements
@@ -469,8 +473,7 @@ int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2
     const int nparts = cn_wgrad_tc_parts(B);
     if (!a1n_ready) cn_a1n_build_kernel<<<dim3((A1 + 31) / 32, B), 256, 0, st>>>(a1, B, a1n);
     cn_conv2_wgrad_tc_kernel<<<nparts, CT_THREADS, WT_SMEM, st>>>(a1n, dz2n, B, wpart);
-    cn_wpart_reduce_kernel<<<C2 * C1 * 9 / 64, 256, 0, st>>>(wpart, nparts, scale, grads);
-    cn_db2_kernel<<<C2, 256, 0, st>>>(dp2, B, scale, grads);
+    cn_wpart_reduce_kernel<<<C2 * C1 * 9 / 64 + C2, 256, 0, st>>>(wpart, nparts, dp2, B, scale, grads);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }
