@@ -96,8 +96,9 @@ int launch_cn_conv2_tc(const float* w2t, const float* params, const float* a1n, 
 int launch_cn_conv2_dgrad_tc(const float* w2d, const float* dp2, const uint8_t* pflag, const float* a1, int B, float* dz2n,
                              float* dz1, cudaStream_t st);
 
-int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
-                             int a1n_ready, float* wpart, float* grads, cudaStream_t st);
+int cn_wgrad_tc_parts(int B);
+int launch_cn_conv2_wgrad_tc(const float* a1, const float* dz2n, int B, float* a1n, int a1n_ready, float* wpart,
+                             cudaStream_t st);
 
 int launch_cn_fc1_fwd_tc(const float* params, const float* p2d, int B, float* part, cudaStream_t st);
 

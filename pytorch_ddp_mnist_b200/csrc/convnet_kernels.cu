@@ -617,13 +617,58 @@ cn_conv1_bwd_kernel(const uint8_t* __restrict__ images, int64_t n_samples, const
     }
 }
 
+// db2[co] = scale . sum of the channel's pooled gradients over the batch (fixed order)
+__device__ __forceinline__ void db2_block(const float* __restrict__ dp2, int B, float scale, float* __restrict__ grads, int co) {
+    __shared__ float red[256];
+    const int tid = threadIdx.x;
+    float v = 0.f;
+#pragma unroll 8
+    for (int i = tid; i < B * NPOOL; i += 256) {
+        const int b = i / NPOOL, p = i - b * NPOOL;
+        v += dp2[(size_t)b * FEAT + (size_t)co * NPOOL + p];
+    }
+    red[tid] = v;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) red[tid] += red[tid + s];
+        __syncthreads();
+    }
+    if (tid == 0) grads[OFF_C2B + co] = red[0] * scale;
+}
+
+
+// sum of the tensor-core weight-gradient kernel's per-CTA partials: four quarter-sums (partials in CTA order) per
+// element, combined in fixed order; 64 elements per block
+__device__ __forceinline__ void wpart_reduce_block(const float* __restrict__ wpart, int nparts, float scale,
+                                                   float* __restrict__ grads, int blk) {
+    __shared__ float red4[4][64];
+    const int jl = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const int j = blk * 64 + jl;
+    const int per = (nparts + 3) / 4, c0 = grp * per, c1 = min(nparts, c0 + per);
+    float v = 0.f;
+#pragma unroll 8
+    for (int c = c0; c < c1; ++c) v += wpart[(size_t)c * (C2 * C1 * 9) + j];
+    red4[grp][jl] = v;
+    __syncthreads();
+    if (grp == 0) grads[OFF_C2W + j] = ((red4[0][jl] + red4[1][jl]) + (red4[2][jl] + red4[3][jl])) * scale;
+}
+
 // sum of the per-image partial gradients and the three small gradients of the dense layers (fc1.bias, fc2.weight,
 // fc2.bias: sums over the batch of dzf, dlogits x hd, dlogits).  One warp per output element: lane l takes images
 // l, l+32, ... (in order), then the 32 lane sums are combined by a fixed shuffle tree - the same order every run.
 constexpr int SMALL_N = FC + NC * FC + NC;                 // 1418
 __global__ void __launch_bounds__(256)
 cn_reduce_kernel(const float* __restrict__ gpart, const float* __restrict__ dzf, const float* __restrict__ dlog,
-                 const float* __restrict__ hd, int B, float scale, int nconv, float* __restrict__ grads) {
+                 const float* __restrict__ hd, int B, float scale, int nconv, float* __restrict__ grads,
+                 const float* __restrict__ wpart, int nparts, const float* __restrict__ dp2, int first_tc_block) {
+    // tensor-core backward: the blocks from first_tc_block on finish conv2's gradients (288 blocks sum the weight-
+    // gradient partials, 64 form the bias gradient) - same launch as the other reductions
+    if ((int)blockIdx.x >= first_tc_block) {
+        const int blk = blockIdx.x - first_tc_block;
+        if (blk < C2 * C1 * 9 / 64) wpart_reduce_block(wpart, nparts, scale, grads, blk);
+        else db2_block(dp2, B, scale, grads, blk - C2 * C1 * 9 / 64);
+        return;
+    }
     const int lane = threadIdx.x & 31;
     const int e = blockIdx.x * 8 + (threadIdx.x >> 5);     // 8 elements per block
     if (e >= nconv + SMALL_N) return;
@@ -796,15 +841,18 @@ extern "C" int ddpm_cn_step_backward(const float* d_params, const uint8_t* d_ima
         const int ready = (flags & DDPM_CN_BWD_FWD_WAS_TF32) ? 1 : 0;
         if (!ready && launch_cn_w2_prep(d_params, (float*)(ws + L.w2t), w2d, st)) return 1;
         if (launch_cn_conv2_dgrad_tc(w2d, dp2, pflag, a1, batch, dz2n, dz1, st)) return 1;
-        if (launch_cn_conv2_wgrad_tc(a1, dp2, dz2n, batch, grad_scale, (float*)(ws + L.a1n), ready, (float*)(ws + L.wpart), d_grads, st)) return 1;
+        if (launch_cn_conv2_wgrad_tc(a1, dz2n, batch, (float*)(ws + L.a1n), ready, (float*)(ws + L.wpart), st)) return 1;
     } else {
         cn_conv2_wgrad_kernel<<<dim3(batch, 2), 256, WG_SMEM, st>>>(a1, dp2, pflag, gpart);
         cn_conv2_dgrad_kernel<<<dim3(batch, 2), DG_THREADS, DG_SMEM, st>>>(d_params, a1, dp2, pflag, dz1);
     }
     cn_conv1_bwd_kernel<<<batch, C1B_THREADS, C1B_SMEM, st>>>(d_images, n_samples, d_idx, dz1, gpart);
     const int nconv = tc ? OFF_C2W : CONV_GRADS;            // conv2's gradients came from the tensor-core kernels
-    cn_reduce_kernel<<<(nconv + SMALL_N + 7) / 8, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog),
-                                                              (const float*)(ws + L.hd), batch, grad_scale, nconv, d_grads);
+    const int red_blocks = (nconv + SMALL_N + 7) / 8;
+    const int tc_blocks = tc ? C2 * C1 * 9 / 64 + C2 : 0;
+    cn_reduce_kernel<<<red_blocks + tc_blocks, 256, 0, st>>>(gpart, dzf, (const float*)(ws + L.dlog), (const float*)(ws + L.hd),
+                                                            batch, grad_scale, nconv, d_grads, (const float*)(ws + L.wpart),
+                                                            tc ? cn_wgrad_tc_parts(batch) : 0, dp2, red_blocks);
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }

@@ -330,25 +330,6 @@ cn_a1n_build_kernel(const float* __restrict__ a1, int B, float* __restrict__ a1n
         if (p0 + r < A1) a1n[((size_t)b * A1 + p0 + r) * C1 + tx] = to_tf32(t[tx][r]);
 }
 
-// db2[co] = scale . sum of the channel's pooled gradients over the batch (fixed order)
-__device__ __forceinline__ void db2_block(const float* __restrict__ dp2, int B, float scale, float* __restrict__ grads, int co) {
-    __shared__ float red[256];
-    const int tid = threadIdx.x;
-    float v = 0.f;
-#pragma unroll 8
-    for (int i = tid; i < B * NPOOL; i += 256) {
-        const int b = i / NPOOL, p = i - b * NPOOL;
-        v += dp2[(size_t)b * FEAT + (size_t)co * NPOOL + p];
-    }
-    red[tid] = v;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if (tid < s) red[tid] += red[tid + s];
-        __syncthreads();
-    }
-    if (tid == 0) grads[OFF_C2B + co] = red[0] * scale;
-}
-
 constexpr int WT_B_BYTES = 2 * CT_A_TILE;                // dz2 rows: two channel halves of 128 positions x 128 B
 constexpr size_t WT_SMEM = (size_t)CT_A_BYTES + WT_B_BYTES + 64 + 1024;
 constexpr uint32_t WT_IDESC = umma_idesc_tf32(128, 64) | (1u << 15) | (1u << 16);      // a_major = b_major = MN
@@ -436,33 +417,13 @@ cn_conv2_wgrad_tc_kernel(const float* __restrict__ a1n, const float* __restrict_
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem_base) : "memory");
 }
 
-// sum of the CTAs' partial weight gradients: four quarter-sums (partials in CTA order) per element, combined in fixed order
-__global__ void __launch_bounds__(256)
-cn_wpart_reduce_kernel(const float* __restrict__ wpart, int nparts, const float* __restrict__ dp2, int B, float scale,
-                       float* __restrict__ grads) {
-    if (blockIdx.x >= C2 * C1 * 9 / 64) {                  // the last 64 blocks: conv2.bias (same launch, one dependency less)
-        db2_block(dp2, B, scale, grads, blockIdx.x - C2 * C1 * 9 / 64);
-        return;
-    }
-    __shared__ float red[4][64];
-    const int jl = threadIdx.x & 63, grp = threadIdx.x >> 6;
-    const int j = blockIdx.x * 64 + jl;                     // 288 blocks x 64 elements
-    const int per = (nparts + 3) / 4, c0 = grp * per, c1 = min(nparts, c0 + per);
-    float v = 0.f;
-#pragma unroll 8
-    for (int c = c0; c < c1; ++c) v += wpart[(size_t)c * (C2 * C1 * 9) + j];
-    red[grp][jl] = v;
-    __syncthreads();
-    if (grp == 0) grads[OFF_C2W + j] = ((red[0][jl] + red[1][jl]) + (red[2][jl] + red[3][jl])) * scale;
-}
-
 int cn_wgrad_tc_parts(int B) {
     const int ntiles = (B * H2 * H2 + 127) / 128;
     return ntiles < 148 ? ntiles : 148;
 }
 
-int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2n, int B, float scale, float* a1n,
-                             int a1n_ready, float* wpart, float* grads, cudaStream_t st) {
+int launch_cn_conv2_wgrad_tc(const float* a1, const float* dz2n, int B, float* a1n, int a1n_ready, float* wpart,
+                             cudaStream_t st) {
     static bool configured[64] = {};
     int dev = 0;
     DDPM_CUDA(cudaGetDevice(&dev));
@@ -473,7 +434,7 @@ int launch_cn_conv2_wgrad_tc(const float* a1, const float* dp2, const float* dz2
     const int nparts = cn_wgrad_tc_parts(B);
     if (!a1n_ready) cn_a1n_build_kernel<<<dim3((A1 + 31) / 32, B), 256, 0, st>>>(a1, B, a1n);
     cn_conv2_wgrad_tc_kernel<<<nparts, CT_THREADS, WT_SMEM, st>>>(a1n, dz2n, B, wpart);
-    cn_wpart_reduce_kernel<<<C2 * C1 * 9 / 64 + C2, 256, 0, st>>>(wpart, nparts, dp2, B, scale, grads);
+    // (the partials are summed, and conv2.bias's gradient formed, by extra blocks of cn_reduce_kernel)
     DDPM_CUDA(cudaGetLastError());
     return 0;
 }
