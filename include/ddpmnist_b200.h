@@ -242,7 +242,7 @@ int  ddpm_train_steps_host_fed(ddpm_feed* feed, ddpm_comm* comm, float* d_params
 #define DDPM_CN_OFF_FC2_W    1198592
 #define DDPM_CN_OFF_FC2_B    1199872
 #define DDPM_CN_MAX_BATCH    8192
-size_t ddpm_cn_workspace_bytes(int max_batch);               /* 0 if max_batch is out of range; ~370 KB per image */
+size_t ddpm_cn_workspace_bytes(int max_batch);               /* 0 if max_batch is out of range; ~0.66 MB per image + 11 MB */
 int ddpm_cn_workspace_init(void* d_workspace, int max_batch, void* stream);
 /* Forward (+ loss).  d_mask1 u8[batch][9216] / d_mask2 u8[batch][128]: injected dropout keep masks
  * (both or neither); DDPM_FWD_PHILOX_MASK: masks from Philox4x32-10 at (seed, step); neither: eval

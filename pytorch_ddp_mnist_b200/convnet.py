@@ -32,7 +32,7 @@ def init_params_like_torch() -> Dict[str, torch.Tensor]:
 
 
 class ConvNetWorkspace:
-    """Caller-owned scratch of the ConvNet step (ddpm_cn_workspace_bytes: ~370 KB per image)."""
+    """Caller-owned scratch of the ConvNet step (ddpm_cn_workspace_bytes: ~0.66 MB per image + 11 MB)."""
 
     def __init__(self, max_batch: int, device):
         self.max_batch = int(max_batch)
