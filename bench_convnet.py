@@ -73,6 +73,50 @@ FLOP_FWD, FLOP_BWD = 23_984_896, 47_580_416          # per image, SURVEY.md §8(
 CONV2_FLOP = 21_233_664                              # conv2 forward = conv2 dgrad = conv2 wgrad (dense), per image
 
 
+def quick_record(torch, dev, B, world, rank, dist, steps=150, warmup=10):
+    """Short resident-data measurement of the json_convnet step for the `context.json_convnet` sub-record of the default
+    bench line (so that the driver's BENCH/SCALE records carry a ConvNet number at all).  TF32 tensor-core path,
+    weak scaling with the NCCL bucket all-reduce at ws > 1; CUDA events, max over ranks."""
+    import numpy as np
+    from pytorch_ddp_mnist_b200 import convnet as cn, synth
+    from pytorch_ddp_mnist_b200.dataset import ResidentDataset
+    N = 60_000
+    im, lb = synth.synth(N, 20260212)
+    res = ResidentDataset.from_arrays(im, lb, dev)
+    g = torch.Generator().manual_seed(7 + rank)
+    idx = torch.randint(0, N, ((steps + warmup) * B,), generator=g, dtype=torch.int64).to(dev)
+    eng = cn.ConvNetEngine(dev, B, world_size=world, rank=rank, tf32=True)
+    torch.manual_seed(0)
+    eng.load_state_dict(cn.init_params_like_torch())
+    eng.broadcast_params()
+    for t in range(warmup):
+        eng.train_step(res, idx[t * B:(t + 1) * B])
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for t in range(warmup, warmup + steps):
+        eng.train_step(res, idx[t * B:(t + 1) * B])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        tt = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    loss = eng.last_batch_loss()
+    peak = _tf32_peak(torch, dev)
+    step_s = ms * 1e-3 / steps
+    tfl = (FLOP_FWD + FLOP_BWD) * B / step_s / 1e12
+    return {"model": "json_convnet (BASELINE.json's ConvNet; NOT in the reference, oracle = restatement, parity unpinned)",
+            "value": steps * B * world / (ms * 1e-3), "unit": "images/s", "batch_per_rank": B, "steps": steps,
+            "us_per_step": 1e6 * step_s, "dtype": "tf32", "final_batch_loss": loss,
+            "roofline": {"bound": "tensor", "achieved": tfl, "peak": peak, "unit": "TFLOP/s", "frac": tfl / peak,
+                         "peak_source": "cuBLAS TF32 matmul 8192^3 measured here, best of 10"},
+            "full_line": "python bench.py --model json_convnet"}
+
+
 def run(args, clock_sampler_cls, peaks_fn, metric) -> None:
     import numpy as np
     import torch

@@ -144,6 +144,11 @@ int ddpm_train_steps_persistent(float* d_params, float* d_grads,
                                 int batch, int nsteps, unsigned flags, float grad_scale, float lr,
                                 float* d_loss, float* d_loss_steps, void* d_workspace, void* stream);
 
+/* Measurement aid (no counterpart in the reference): `nlaunches` cooperative launches of an EMPTY kernel with the
+ * step kernel's launch shape (148 blocks x 256 threads, same dynamic shared memory) on `stream`.  bench.py times
+ * it as the launch floor that SURVEY.md §8(d) asks to be reported beside the step time. */
+int ddpm_persist_launch_floor(int nlaunches, void* stream);
+
 /* -------------------------------------------------------------------------------- fused data-parallel step
  * DistributedDataParallel's gradient averaging (mp:439: one 473,088-byte bucket, pre-divided by
  * world_size, summed over ranks) + optimizer.step() (mp:463), done INSIDE the persistent step

@@ -22,6 +22,7 @@ Fixtures (all small, .npz, committed):
                  step 0 / 1 / 100, packed dropout masks.
   traj_ws2.npz   same loop on 2 gloo ranks (20 steps): per-rank indices and losses, step-0
                  averaged grads, final params.
+  traj_ws4.npz, traj_ws8.npz   the same on 4 and 8 gloo ranks (1 thread each).
   main_e2e.npz   the reference's `main()` itself, unmodified, `--parallel --wireup_method gloo
                  --batch_size 64 --n_epochs 2` on a 4000/1000-sample dataset: the printed
                  `Epoch=…` lines and the final state_dict.
@@ -81,7 +82,7 @@ def _init_pg(rank, ws, port):
 # ----------------------------------------------------------------------------- trajectory runs
 def run_traj(rank, ws, port, data_dir, steps, batch, out_q=None):
     """The reference's loop body (`mp:453-466`) with the reference's own objects, instrumented."""
-    torch.set_num_threads(4)
+    torch.set_num_threads(4 if ws <= 2 else 1)
     torch.use_deterministic_algorithms(True)
     os.chdir(data_dir)
     ref = _import_reference()
@@ -158,31 +159,37 @@ def gen_traj_ws1(out_dir, data_dir):
     print("traj_ws1: loss[0]=%.6f loss[99]=%.6f" % (o["losses"][0], o["losses"][-1]))
 
 
-def gen_traj_ws2(out_dir, data_dir):
+def gen_traj_ws(out_dir, data_dir, ws, port):
+    """`ws` gloo ranks of the reference loop, 20 steps: per-rank indices, losses and masks; step-0 averaged
+    gradients; initial and final parameters (asserted identical on every rank, as DDP guarantees)."""
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    ps = [ctx.Process(target=run_traj, args=(r, 2, 29612, data_dir, 20, 64, q)) for r in range(2)]
+    ps = [ctx.Process(target=run_traj, args=(r, ws, port, data_dir, 20, 64, q)) for r in range(ws)]
     for p in ps:
         p.start()
     res = dict(q.get() for _ in ps)
     for p in ps:
         p.join()
     flat = {}
-    for r in range(2):
+    for r in range(ws):
         o = res[r]
         keep = {"losses": o["losses"], "idx": o["idx"], "masks": o["masks"],
                 "shard_head": o["shard_head"], "shard_len": o["shard_len"]}
         _flatten(f"rank{r}.", keep, flat)
-    for k in res[0]["paramsN"]:                     # DDP keeps the replicas identical
-        assert np.array_equal(res[0]["paramsN"][k], res[1]["paramsN"][k]), k
-        assert np.array_equal(res[0]["params0"][k], res[1]["params0"][k]), k
-        assert np.array_equal(res[0]["grads0"][k], res[1]["grads0"][k]), k
+    for r in range(1, ws):
+        for k in res[0]["paramsN"]:                 # DDP keeps the replicas identical
+            assert np.array_equal(res[0]["paramsN"][k], res[r]["paramsN"][k]), k
+            assert np.array_equal(res[0]["params0"][k], res[r]["params0"][k]), k
+            assert np.array_equal(res[0]["grads0"][k], res[r]["grads0"][k]), k
     _flatten("", {"grads0": res[0]["grads0"], "params0": res[0]["params0"],
                   "paramsN": res[0]["paramsN"]}, flat)
-    np.savez_compressed(os.path.join(out_dir, "traj_ws2.npz"), **flat)
-    print("traj_ws2: rank0 loss[0]=%.6f rank1 loss[0]=%.6f" %
-          (res[0]["losses"][0], res[1]["losses"][0]))
+    np.savez_compressed(os.path.join(out_dir, f"traj_ws{ws}.npz"), **flat)
+    print(f"traj_ws{ws}: " + " ".join("rank%d loss[0]=%.6f" % (r, res[r]["losses"][0]) for r in range(ws)))
+
+
+def gen_traj_ws2(out_dir, data_dir):
+    gen_traj_ws(out_dir, data_dir, 2, 29612)
 
 
 # ----------------------------------------------------------------------------- unmodified main()
@@ -283,9 +290,9 @@ def main():
     os.makedirs(a.out, exist_ok=True)
     if not os.path.isdir(REF_DIR):
         raise SystemExit("gen_golden.py needs /root/reference (build container only)")
-    todo = a.only.split(",") if a.only else ["kats", "traj_ws1", "traj_ws2", "main_e2e"]
+    todo = a.only.split(",") if a.only else ["kats", "traj_ws1", "traj_ws2", "traj_ws4", "traj_ws8", "main_e2e"]
     with tempfile.TemporaryDirectory() as data_dir:
-        if {"traj_ws1", "traj_ws2"} & set(todo):
+        if {"traj_ws1", "traj_ws2", "traj_ws4", "traj_ws8"} & set(todo):
             synth.write_default_files(data_dir)
         if "kats" in todo:
             gen_kats(a.out)
@@ -293,6 +300,10 @@ def main():
             gen_traj_ws1(a.out, data_dir)
         if "traj_ws2" in todo:
             gen_traj_ws2(a.out, data_dir)
+        if "traj_ws4" in todo:
+            gen_traj_ws(a.out, data_dir, 4, 29614)
+        if "traj_ws8" in todo:
+            gen_traj_ws(a.out, data_dir, 8, 29618)
         if "main_e2e" in todo:
             gen_main_e2e(a.out)
 

@@ -123,32 +123,89 @@ def port_train(root_dir: str, batch_size: int, steps: int, warmup: int, rank: in
             "state": {k: v.detach().clone() for k, v in m.state_dict().items()}}
 
 
-def _worker(rank, world_size, port, root_dir, batch_size, steps, warmup, threads, q):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world_size))
-    torch.set_num_threads(max(1, threads))
-    dist.init_process_group("gloo", init_method="env://", rank=rank, world_size=world_size)
-    r = port_train(root_dir, batch_size, steps, warmup, rank, world_size)
-    dist.destroy_process_group()
-    q.put((rank, r["seconds"], r["images"], r["loader_seconds"]))
+# Variables a launcher (torchrun / torch.distributed.launch) exports into its workers.  A process spawned from such a
+# worker inherits them; with TORCHELASTIC_USE_AGENT_STORE set, torch's rendezvous makes even rank 0 a *client* of the
+# launcher's store, so a private group built by env:// or tcp:// rendezvous waits for a server nobody starts.
+_LAUNCHER_ENV = ("TORCHELASTIC_", "TORCH_NCCL_", "NCCL_ASYNC", "ROLE_", "GROUP_", "LOCAL_RANK", "LOCAL_WORLD_SIZE",
+                 "RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS")
+
+
+def scrub_launcher_env(env=None):
+    """Remove every launcher-exported variable from `env` (default os.environ); returns the removed names."""
+    env = os.environ if env is None else env
+    gone = [k for k in list(env) if k.startswith(_LAUNCHER_ENV)]
+    for k in gone:
+        del env[k]
+    return gone
+
+
+def _worker(rank, world_size, store_path, root_dir, batch_size, steps, warmup, threads, q):
+    try:
+        scrub_launcher_env()
+        torch.set_num_threads(max(1, threads))
+        # private rendezvous through a file: no TCP port to collide with, nothing read from the environment
+        store = dist.FileStore(store_path, world_size)
+        import datetime
+        dist.init_process_group("gloo", store=store, rank=rank, world_size=world_size,
+                                timeout=datetime.timedelta(seconds=120))
+        r = port_train(root_dir, batch_size, steps, warmup, rank, world_size)
+        dist.destroy_process_group()
+        q.put((rank, r["seconds"], r["images"], r["loader_seconds"], None))
+    except BaseException as e:                        # the parent must hear about it instead of waiting
+        q.put((rank, 0.0, 0, 0.0, repr(e)))
+        raise
 
 
 def time_port_gloo(root_dir: str, batch_size: int, steps: int, warmup: int, world_size: int = 2,
-                   port: int = 29655) -> Dict:
+                   port: int = 0, timeout_s: float = 600.0) -> Dict:
     """BASELINE.json configs[0]: `--parallel --wireup_method gloo --batch_size 64`, world_size
     processes x (cores // world_size) threads; returns global images/s over the timed steps
-    (max over ranks of the wall time, like the GPU arm)."""
+    (max over ranks of the wall time, like the GPU arm).  Safe to call from a torchrun worker: the
+    children drop the launcher's environment and rendezvous through a private FileStore (`port` is
+    unused, kept for callers of the old signature).  Raises RuntimeError (never hangs) if a worker
+    dies or the whole run exceeds `timeout_s`."""
+    import queue as _queue
+    import tempfile
     import torch.multiprocessing as mp
     cores = os.cpu_count() or 1
     threads = max(1, cores // world_size)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    ps = [ctx.Process(target=_worker, args=(r, world_size, port, root_dir, batch_size, steps, warmup, threads, q))
-          for r in range(world_size)]
-    for p in ps:
-        p.start()
-    res = [q.get() for _ in ps]
-    for p in ps:
-        p.join()
+    store_dir = tempfile.mkdtemp(prefix="refport_store_")
+    store_path = os.path.join(store_dir, "store")
+    ps = [ctx.Process(target=_worker, args=(r, world_size, store_path, root_dir, batch_size, steps, warmup, threads, q),
+                      daemon=True) for r in range(world_size)]
+    saved = dict(os.environ)                          # children are spawned with a launcher-free environment
+    scrub_launcher_env()
+    try:
+        for p in ps:
+            p.start()
+    finally:
+        os.environ.update({k: v for k, v in saved.items() if k not in os.environ})
+    res, deadline, err = [], time.monotonic() + timeout_s, None
+    try:
+        while len(res) < world_size and err is None:
+            try:
+                item = q.get(timeout=1.0)
+                if item[4] is not None:
+                    err = f"rank {item[0]} failed: {item[4]}"
+                res.append(item)
+            except _queue.Empty:
+                dead = [p for p in ps if p.exitcode not in (None, 0)]
+                if dead:
+                    err = f"worker exited with code {dead[0].exitcode}"
+                elif time.monotonic() > deadline:
+                    err = f"timed out after {timeout_s:.0f} s"
+    finally:
+        for p in ps:
+            p.join(timeout=5.0 if err is None else 0.5)
+            if p.is_alive():
+                p.terminate()
+                p.join(timeout=5.0)
+        import shutil
+        shutil.rmtree(store_dir, ignore_errors=True)
+    if err is not None:
+        raise RuntimeError(f"time_port_gloo(world_size={world_size}): {err}")
     secs = max(r[1] for r in res)
     imgs = sum(r[2] for r in res)
     return {"images_per_s": imgs / secs, "seconds": secs, "images": imgs, "world_size": world_size,

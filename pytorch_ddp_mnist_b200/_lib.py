@@ -55,6 +55,7 @@ SIGNATURES = {
                                                 _u32, _vp, _vp, _vp]),
     "ddpm_train_steps_persistent": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32,
                                            _f32, _f32, _vp, _vp, _vp, _vp]),
+    "ddpm_persist_launch_floor": (_i32, [_i32, _vp]),
     "ddpm_comm_create": (_i32, [_i32, _i32, C.POINTER(_vp)]),
     "ddpm_comm_ipc_handle": (_i32, [_vp, _vp]),
     "ddpm_comm_connect": (_i32, [_vp, _vp]),

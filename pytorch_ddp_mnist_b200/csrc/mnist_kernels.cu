@@ -86,7 +86,12 @@ static WsLayout ws_layout_compute(int max_batch) {
     L.dz3 = off;     off = al256(off + B * NCP * sizeof(float));
     L.rowloss = off; off = al256(off + B * sizeof(float));
     L.yb = off;      off = al256(off + B);
-    L.gpart = off;   off = al256(off + (grads_bsplit(max_batch) > 1 ? (size_t)grads_bsplit(max_batch) * NP * sizeof(float) : 0));
+    // gpart holds the batch-slice partial gradients of grads_kernel (grads_bsplit slices, capped at 32) AND, on the
+    // tcgen05 path, dw1_tc_kernel's slices (one per 224 rows: 37 at batch 8192, 74 at 16384): size it for the larger
+    // (both counts grow monotonically with the batch, so a workspace sized for max_batch holds every smaller batch)
+    int gslices = grads_bsplit(max_batch) > 1 ? grads_bsplit(max_batch) : 0;
+    if (max_batch >= 2048 && dw1_tc_slices(max_batch) > gslices) gslices = dw1_tc_slices(max_batch);
+    L.gpart = off;   off = al256(off + (size_t)gslices * NP * sizeof(float));
     L.total = off;
     return L;
 }
@@ -1209,6 +1214,8 @@ int ddpm_step_backward(float* d_params,
         // fc1's weight gradient (85 % of the flops of the backward pass) on the tensor cores.  Below 2048 rows the
         // 7 x slices grid leaves most SMs idle and the FFMA tiles are faster (measured: 46 vs 37 us at 1024).
         g.bsplit_w1 = dw1_tc_slices(batch); g.skip_w1 = 1;
+        DDPM_CHECK_ARG(L.gpart + (size_t)g.bsplit_w1 * NP * sizeof(float) <= L.total,
+                       "ddpm_step_backward: batch %d needs %d gradient slices, the workspace layout holds fewer", batch, g.bsplit_w1);
         if (launch_dw1_tc(g.dz1, d_images, n_samples, d_idx, batch, g.gpart, st)) return 1;
     }
     if (d_x == nullptr) grads_kernel<true><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);

@@ -1018,6 +1018,32 @@ static int persist_fill_and_launch(PersistArgs& a, float* d_params, float* d_gra
     return 0;
 }
 
+// Launch floor of the step kernel's launch shape: an empty kernel, same grid / block / dynamic shared memory,
+// launched cooperatively.  What a step can never be faster than per LAUNCH (not per step: a launch runs many steps).
+__global__ void __launch_bounds__(P_THREADS, 1) persist_floor_kernel(int* sink) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (sink != nullptr && threadIdx.x == 0 && blockIdx.x == 0xffffffu) *sink = (int)smem_raw[0];
+}
+
+extern "C" int ddpm_persist_launch_floor(int nlaunches, void* stream) {
+    DDPM_CHECK_ARG(nlaunches > 0 && nlaunches <= 100000, "ddpm_persist_launch_floor: nlaunches %d out of range", nlaunches);
+    if (persist_configure()) return 1;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    DDPM_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        DDPM_CUDA(cudaFuncSetAttribute((const void*)persist_floor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(PersistSmem)));
+        attr_set[dev] = true;
+    }
+    int* sink = nullptr;
+    void* kargs[] = {&sink};
+    for (int i = 0; i < nlaunches; ++i)
+        DDPM_CUDA(cudaLaunchCooperativeKernel((const void*)persist_floor_kernel, dim3(P_GRID), dim3(P_THREADS), kargs,
+                                              sizeof(PersistSmem), (cudaStream_t)stream));
+    return 0;
+}
+
 extern "C" int ddpm_train_steps_persistent(
         float* d_params, float* d_grads,
         const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,

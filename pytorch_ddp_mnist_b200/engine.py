@@ -84,11 +84,27 @@ class TrainEngine:
             import torch.distributed as dist
             dist.broadcast(self.params, src=src, group=self.group)
 
-    def enable_fused_ddp(self) -> None:
+    def enable_fused_ddp(self, strict: bool = True) -> bool:
         """Switch the ws > 1 path from `kernel -> NCCL allreduce -> SGD kernel` per step to the fused
-        kernel (gradient exchange over NVLink peer memory inside the persistent step kernel)."""
-        if self.world_size > 1 and self.comm is None:
-            self.comm = ops.FusedComm(self.rank, self.world_size, self.group)
+        kernel (gradient exchange over NVLink peer memory inside the persistent step kernel).  Collective.
+        The fused exchange needs all ranks on one host, world <= 8 and peer access between every pair of GPUs;
+        with `strict=False` a job that cannot have it (multi-node SLURM/MPI wire-ups, > 8 ranks, no P2P) keeps the
+        NCCL path on every rank and this returns False after a one-line notice on rank 0."""
+        if self.world_size <= 1 or self.comm is not None:
+            return self.comm is not None
+        ok, why = ops.FusedComm.usable(self.world_size, self.group)
+        if ok:
+            try:
+                self.comm = ops.FusedComm(self.rank, self.world_size, self.group)
+                return True
+            except ops._lib.DDPMError as e:               # agreed on by all ranks inside FusedComm
+                ok, why = False, str(e)
+        if strict:
+            raise RuntimeError(f"fused data-parallel step unavailable: {why}")
+        if self.rank == 0:
+            print(f"pytorch_ddp_mnist_b200: in-kernel gradient exchange unavailable ({why}); "
+                  f"using NCCL all-reduce between kernels")
+        return False
 
     def check_comm(self) -> None:
         if self.comm is not None and self.comm.error():

@@ -41,7 +41,11 @@ class _MLPFunction(torch.autograd.Function):
             module._train_forwards += 1
         need_bwd = any(ctx.needs_input_grad)          # grad mode is off inside Function.forward
         ops.step_forward(flat, ws, b, x=x, prep_backward=need_bwd, logits=logits, **kw)
-        ctx.module, ctx.batch = module, b
+        # the activations backward needs live in the module's ONE workspace, not in ctx: stamp this forward so that a
+        # backward which comes after another forward (validation inside the step, micro-batches, two losses) fails
+        # loudly instead of returning the gradients of the wrong batch
+        module._fwd_generation += 1
+        ctx.module, ctx.batch, ctx.generation = module, b, module._fwd_generation
         ctx.save_for_backward(x)
         return logits
 
@@ -49,6 +53,10 @@ class _MLPFunction(torch.autograd.Function):
     def backward(ctx, dlogits):
         (x,) = ctx.saved_tensors
         m = ctx.module
+        if m._fwd_generation != ctx.generation:
+            raise RuntimeError("pytorch_ddp_mnist_b200: backward() of a forward pass whose activations were overwritten by "
+                               "a later forward of the same model (the model keeps one workspace: call backward() "
+                               "before the next model(x), as the reference's loop does, mp:460-462)")
         g = torch.empty(N_PARAMS, dtype=torch.float32, device=x.device)
         ops.step_backward(m._flat, m._workspace(ctx.batch), ctx.batch, x=x,
                           dlogits=dlogits.contiguous().float(), grads=g)
@@ -74,6 +82,7 @@ class B200MLP(nn.Sequential):
         self._train_forwards = 0
         self._seed = 42
         self._last_grads = None
+        self._fwd_generation = 0
 
     # ---- flat storage ------------------------------------------------------------------
     def _param_list(self):

@@ -169,23 +169,69 @@ def train_steps_persistent(params: torch.Tensor, ws: Workspace, batch: int, nste
                                           ptr(loss), ptr(loss_steps), ptr(ws.buf), cur_stream()))
 
 
+def launch_floor(nlaunches: int = 1) -> None:
+    """`nlaunches` empty cooperative launches with the step kernel's launch shape (measurement aid)."""
+    check(lib.ddpm_persist_launch_floor(int(nlaunches), cur_stream()))
+
+
 class FusedComm:
     """Communicator of the fused data-parallel step (ddpm_comm_*): a symmetric device buffer per
     rank, mapped into every peer process with CUDA IPC.  Handles travel over torch.distributed."""
 
     def __init__(self, rank: int, world: int, group=None):
+        """Collective over `group`.  Every failure point is followed by an agreement step (all-reduce of a success
+        flag), so either every rank gets a connected communicator or every rank raises `DDPMError` - no rank is
+        left waiting in a collective for a peer that gave up."""
         import ctypes as C
         import torch.distributed as dist
         self.rank, self.world = rank, world
         self._h = C.c_void_p()
-        check(lib.ddpm_comm_create(rank, world, C.byref(self._h)))
+        dev = torch.device("cuda", torch.cuda.current_device())
+
+        def agree(ok: bool, what: str, err: str = ""):
+            flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if not bool(flag.item()):
+                self.close()
+                raise _lib.DDPMError(f"fused data-parallel communicator: {what} failed on "
+                                     f"{'this rank: ' + err if not ok else 'another rank'}")
+
+        err = ""
+        ok = lib.ddpm_comm_create(rank, world, C.byref(self._h)) == 0
+        if not ok:
+            err, self._h = _lib.last_error(), C.c_void_p()
+        agree(ok, "ddpm_comm_create", err)
         mine = (C.c_ubyte * 64)()
-        check(lib.ddpm_comm_ipc_handle(self._h, mine))
+        ok = lib.ddpm_comm_ipc_handle(self._h, mine) == 0
+        agree(ok, "ddpm_comm_ipc_handle", "" if ok else _lib.last_error())
         gathered = [None] * world
         dist.all_gather_object(gathered, bytes(mine), group=group)
         blob = (C.c_ubyte * (64 * world)).from_buffer_copy(b"".join(gathered))
-        check(lib.ddpm_comm_connect(self._h, blob))
+        ok = lib.ddpm_comm_connect(self._h, blob) == 0
+        agree(ok, "ddpm_comm_connect (CUDA IPC mapping of a peer's buffer)", "" if ok else _lib.last_error())
         dist.barrier(group=group)                         # everyone is mapped before anyone launches
+
+    @staticmethod
+    def usable(world: int, group=None) -> Tuple[bool, str]:
+        """Collective: can this job use the in-kernel exchange?  It needs every rank on ONE host (CUDA IPC), at most
+        8 ranks (one NVLink domain) and peer access between every pair of the job's GPUs.  All ranks return the same
+        answer; the string says why not."""
+        import socket
+        import torch.distributed as dist
+        if world > 8:
+            return False, f"world size {world} > 8"
+        me = (socket.gethostname(), torch.cuda.current_device())
+        everyone = [None] * world
+        dist.all_gather_object(everyone, me, group=group)
+        if len({h for h, _ in everyone}) != 1:
+            return False, "ranks span more than one host"
+        mine = me[1]
+        ok = all(d == mine or torch.cuda.can_device_access_peer(mine, d) for _, d in everyone)
+        if len({d for _, d in everyone}) != world:
+            ok = False                                    # two ranks on one GPU
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=torch.device("cuda", mine))
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return (True, "") if bool(flag.item()) else (False, "no peer access between some pair of GPUs")
 
     def error(self) -> int:
         import ctypes as C

@@ -77,9 +77,9 @@ def init_parallel(config):
     rank, world_size = 0, 1
     if config["trainer"]["parallel"]:
         method = config["trainer"]["wireup_method"]
-        if method == "gloo":
-            method = "nccl-mpich"            # same env discovery, NCCL transport: the data is on the GPUs
-        comm = wireup.distributed(method)
+        # `gloo`: the reference's gloo env discovery (OMPI_COMM_WORLD_* / PMIx / PMI, mp:213-254) is kept; only the
+        # transport becomes NCCL, because the data is on the GPUs
+        comm = wireup.distributed(method, backend="nccl" if method == "gloo" else None)
         rank, world_size, local_rank = comm.get_rank(), comm.get_size(), comm.get_local_rank()
     else:
         comm, local_rank = None, config["trainer"]["device"]
@@ -122,7 +122,8 @@ def main(model: nn.Module, train_loader: DeviceBatchLoader, test_loader: DeviceB
     eng.load_state_dict(model.state_dict())
     eng.broadcast_params(0)                              # DistributedDataParallel(model), mp:439
     if world_size > 1 and batch <= 512:
-        eng.enable_fused_ddp()                           # gradient average inside the step kernel (NVLink peer memory)
+        eng.enable_fused_ddp(strict=False)               # gradient average inside the step kernel (NVLink peer memory)
+                                                         # when the job is one host, <= 8 ranks, all-pairs P2P; else NCCL
     train_res, test_res = train_loader.resident, test_loader.resident
     step_no = 0
     for i in range(epochs):

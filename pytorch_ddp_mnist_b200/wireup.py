@@ -101,9 +101,11 @@ class distributed:
     """Same surface as the reference class: `distributed(method)`, `get_size()`, `get_rank()`,
     `get_local_rank()`, `barrier()`, `reduceMAX()`, `finalize()`."""
 
-    def __init__(self, method: str):
+    def __init__(self, method: str, backend: str = None):
+        """`backend` overrides the transport the reference ties to `method` (train.py runs the `gloo` wire-up -
+        its OMPI_COMM_WORLD_* / PMIx / PMI discovery, mp:213-254 - over NCCL, because the data lives on GPUs)."""
         discover_env(method)
-        backend = _BACKEND[method]
+        backend = backend or _BACKEND[method]
         if backend == "mpi" and not dist.is_mpi_available():
             raise NotImplementedError("wireup_method 'mpich' needs a torch build with the MPI backend; "
                                       "use 'gloo' or one of the nccl-* methods")

@@ -1,8 +1,11 @@
-"""Run under torchrun with 2 ranks (tests/test_gpu_train.py::test_multi_gpu_ddp_matches_reference_ws2):
-the engine's DDP path (pre-divided flat bucket + NCCL allreduce SUM + flat SGD) against the
-reference's own 2-rank gloo run recorded in tests/golden/traj_ws2.npz."""
+"""Run under torchrun with 2, 4 or 8 ranks (tests/test_gpu_train.py::test_multi_gpu_ddp_matches_reference and
+`bench.py`'s parity gate use the same code): every data-parallel step path against the reference's own gloo
+run at the same world size (tests/golden/traj_ws{2,4,8}.npz), plus what the gate does not cover — a second fused
+launch on the same communicator, the drop-in `create_model()` under `DistributedDataParallel`, the slab +
+all-gather dataset loader, and the BASELINE.json ConvNet's bucket all-reduce."""
 import os
 import sys
+import tempfile
 
 import numpy as np
 import torch
@@ -10,10 +13,78 @@ import torch.distributed as dist
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tests"))
 
 from oracle import mnist_oracle as O                      # noqa: E402
 from pytorch_ddp_mnist_b200 import engine as E, synth     # noqa: E402
 from pytorch_ddp_mnist_b200.dataset import ResidentDataset  # noqa: E402
+import parity_gate                                        # noqa: E402
+
+
+def check_ddp_wrapped_model(rank, world, local, dev, g):
+    """tg:72 / mp:439: `DistributedDataParallel(create_model().to(dev), device_ids=[rank])` over the drop-in
+    model, driven by the reference's loop body (mp:455-465) textually, against the reference's gloo run."""
+    from torch.nn.parallel import DistributedDataParallel
+    from pytorch_ddp_mnist_b200 import model as M, ops
+    im, lb = synth.synth(synth.TRAIN_N, synth.TRAIN_SEED)
+    images = torch.from_numpy(im.reshape(-1, 784)).to(dev)
+    labels = torch.from_numpy(lb).to(dev)
+    torch.manual_seed(100 + rank)                          # ranks start different, the wrap broadcasts rank 0's
+    model = M.create_model()
+    if rank == 0:
+        model.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
+    model = model.to(dev)
+    masks = torch.from_numpy(O.unpack_masks(g[f"rank{rank}.masks"])).to(dev)
+    model.set_mask_provider(lambda t, b: masks[t])
+    model = DistributedDataParallel(model, device_ids=[local], output_device=local)
+    for k, v in model.module.state_dict().items():
+        assert np.array_equal(v.cpu().numpy(), g[f"params0.{k}"]), ("DDP wrap did not adopt rank 0's parameters", k)
+    optimizer = M.SGD(model.parameters(), lr=0.01)
+    loss = M.CrossEntropyLoss()
+    model.train()
+    idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
+    losses = []
+    for t in range(idx.shape[0]):
+        x, y = ops.gather_decode(images, labels, idx[t])
+        x = x.view(x.shape[0], -1)
+        optimizer.zero_grad()
+        y_hat = model(x)
+        batch_loss = loss(y_hat, y)
+        batch_loss.backward()
+        optimizer.step()
+        losses.append(batch_loss.item())
+    ref = g[f"rank{rank}.losses"]
+    err = np.abs(np.array(losses) - ref).max()
+    assert err < 5e-3 * np.abs(ref).max(), ("DDP-wrapped model: loss trajectory", rank, err)
+    assert np.abs(np.array(losses[:3]) - ref[:3]).max() < 1e-5
+    sd = model.module.state_dict()
+    for k in O.PARAM_KEYS:
+        r = g[f"paramsN.{k}"].astype(np.float64)
+        fro = np.linalg.norm(sd[k].cpu().numpy() - r) / np.linalg.norm(r)
+        assert fro < 5e-3, ("DDP-wrapped model: final parameters", k, fro)
+    mine = torch.cat([sd[k].reshape(-1) for k in O.PARAM_KEYS])
+    other = mine.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(mine, other), "DDP-wrapped model: replicas diverged"
+    return float(err)
+
+
+def check_slab_loader(rank, world, dev):
+    """`ResidentDataset.from_file` at ws > 1: every rank reads one contiguous slab of the CDF-5 file and an
+    all-gather replicates the u8 dataset - the result must be the file's bytes on every rank."""
+    n = 10_007                                              # not divisible by the world size: ragged last slab
+    im, lb = synth.synth(n, 77)
+    d = [None]
+    if rank == 0:
+        d[0] = tempfile.mkdtemp(prefix="slab_")
+        from pytorch_ddp_mnist_b200 import cdf5
+        cdf5.write_mnist_cdf5(os.path.join(d[0], "mnist_train_images.nc"), im, lb)
+    dist.broadcast_object_list(d, src=0)
+    res = ResidentDataset.from_file(os.path.join(d[0], "mnist_train_images.nc"), dev, rank=rank, world_size=world)
+    assert res.images.shape[0] == n and res.labels.shape[0] == n
+    assert torch.equal(res.images.cpu(), torch.from_numpy(im.reshape(-1, 784))), "slab loader: pixels differ"
+    assert torch.equal(res.labels.cpu(), torch.from_numpy(lb)), "slab loader: labels differ"
+    dist.barrier()
 
 
 def main():
@@ -22,110 +93,38 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", init_method="env://", device_id=dev)
-    g = np.load(os.path.join(REPO, "tests", "golden", "traj_ws2.npz"))
+
+    # ---- every step path vs the reference's gloo run at this world size
+    rec = parity_gate.run_gate(dev, rank, world, dist)
+    assert rec["ok"], rec
+    if world in parity_gate.GOLDEN_WS:
+        assert rec["golden"] and rec["max_loss_err"] is not None
+
     im, lb = synth.synth(synth.TRAIN_N, synth.TRAIN_SEED)
     res = ResidentDataset.from_arrays(im, lb, dev)
-    eng = E.TrainEngine(dev, 64, world_size=world, rank=rank)
-    torch.manual_seed(100 + rank)                          # ranks start different, like the reference
-    eng.load_state_dict(E.init_params_like_reference())
-    if rank == 0:
-        eng.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
-    eng.broadcast_params(0)                                # DDP wrap: everyone adopts rank 0's
-    golden_ws = (world == 2)
-    if golden_ws:
-        masks = torch.from_numpy(O.unpack_masks(g[f"rank{rank}.masks"])).to(dev)
-        idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
+    ddp_err = None
+    if world in parity_gate.GOLDEN_WS:
+        g = np.load(os.path.join(REPO, "tests", "golden", f"traj_ws{world}.npz"))
         assert np.array_equal(g[f"rank{rank}.idx"][0], O.shard_indices(60000, world, rank)[:64])
-        ref = g[f"rank{rank}.losses"]
-    else:                                   # no reference run at this world size: self-consistency only
-        rng = np.random.default_rng(500 + rank)
-        masks = torch.from_numpy((rng.random((20, 64, 128)) < 0.8).astype(np.uint8)).to(dev)
-        idx = torch.from_numpy(O.shard_indices(60000, world, rank)[:20 * 64].reshape(20, 64)).to(dev)
-        ref = None
-    losses = []
-    for t in range(idx.shape[0]):
-        eng.train_step(res, idx[t], mask=masks[t])
-        losses.append(eng.last_batch_loss())
-    err = 0.0
-    if golden_ws:
-        err = np.abs(np.array(losses) - ref).max()
-        assert err < 5e-3 * np.abs(ref).max(), (rank, err)
-        assert np.abs(np.array(losses[:3]) - ref[:3]).max() < 1e-5
-        pu = O.unflatten_params(eng.params.cpu().numpy())
-        for k in O.PARAM_KEYS:
-            r = g[f"paramsN.{k}"].astype(np.float64)
-            fro = np.linalg.norm(pu[k] - r) / np.linalg.norm(r)
-            assert fro < 5e-3, (k, fro)
-    ref = np.array(losses, np.float32)      # the NCCL path is the yardstick for the fused path below
-    # replicas stay bit-identical
-    mine = eng.params.clone()
-    other = mine.clone()
-    dist.broadcast(other, src=0)
-    assert torch.equal(mine, other), "replicas diverged"
-    dist.barrier()
+        # ---- a second launch continues the flag sequence (communicator step counter) and stays in lock-step
+        eng2 = E.TrainEngine(dev, 64, world_size=world, rank=rank)
+        eng2.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
+        eng2.enable_fused_ddp()
+        idx = torch.from_numpy(g[f"rank{rank}.idx"]).to(dev)
+        idx_all = torch.from_numpy(np.stack([g[f"rank{r}.idx"].reshape(-1) for r in range(world)])).to(dev)
+        for n0, n1 in ((0, 7), (7, 20), (0, 4)):
+            eng2.train_steps(res, idx[n0:n1].reshape(-1).contiguous(), 64, n1 - n0,
+                             idx_all=idx_all[:, n0 * 64:n1 * 64].contiguous())
+            torch.cuda.synchronize()
+            eng2.check_comm()
+            mine = eng2.params.clone()
+            other = mine.clone()
+            dist.broadcast(other, src=0)
+            assert torch.equal(mine, other), "fused replicas diverged after a follow-up launch"
+        dist.barrier()
+        ddp_err = check_ddp_wrapped_model(rank, world, local, dev, g)
+    check_slab_loader(rank, world, dev)
 
-    # ---- fused path: the same 20 steps in ONE launch per rank, gradients exchanged over peer memory
-    eng2 = E.TrainEngine(dev, 64, world_size=world, rank=rank)
-    eng2.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
-    eng2.enable_fused_ddp()
-    ls = torch.zeros(idx.shape[0], device=dev)
-    # every rank's batches: fc1's gradient then goes through the dz1 exchange (DDPM_NO_ACT_EXCHANGE=1 keeps the
-    # full gradient exchange; both are exercised by the callers of this script)
-    if golden_ws:
-        all_np = np.stack([g[f"rank{r}.idx"].reshape(-1) for r in range(world)])
-    else:
-        all_np = np.stack([O.shard_indices(60000, world, r)[:20 * 64] for r in range(world)])
-    idx_all = torch.from_numpy(np.ascontiguousarray(all_np)).to(dev)
-    assert torch.equal(idx_all[rank], idx.reshape(-1))
-    eng2.train_steps(res, idx.reshape(-1).contiguous(), 64, idx.shape[0], masks=masks.contiguous(), loss_steps=ls,
-                     idx_all=idx_all)
-    torch.cuda.synchronize()
-    eng2.check_comm()
-    l2 = ls.cpu().numpy()
-    assert np.abs(l2 - ref).max() < 1e-4 * np.abs(ref).max(), (rank, np.abs(l2 - ref).max())
-    assert np.abs(l2[:3] - ref[:3]).max() < 1e-5
-    rel = float((eng2.params - eng.params).abs().max() / eng.params.abs().max())
-    assert rel < 1e-4, ("fused vs NCCL path", rel)            # same math, different summation order
-    mine = eng2.params.clone()
-    other = mine.clone()
-    dist.broadcast(other, src=0)
-    assert torch.equal(mine, other), "fused replicas diverged"
-    p20 = eng2.params.clone()
-    # a second launch continues the flag sequence (communicator step counter) and stays in lock-step
-    eng2.train_steps(res, idx[:4].reshape(-1).contiguous(), 64, 4, idx_all=idx_all[:, :4 * 64].contiguous())
-    torch.cuda.synchronize()
-    eng2.check_comm()
-    mine = eng2.params.clone()
-    other = mine.clone()
-    dist.broadcast(other, src=0)
-    assert torch.equal(mine, other), "fused replicas diverged after the second launch"
-    dist.barrier()
-
-    # ---- host-fed fused loop: this rank's batches stream from pinned host memory (ring of 8 slots: reuse + wrap),
-    # gradients averaged inside the kernel (full bucket exchange: other ranks' pixels are not on this device)
-    eng3 = E.TrainEngine(dev, 64, world_size=world, rank=rank)
-    eng3.load_state_dict({k: torch.from_numpy(g[f"params0.{k}"]) for k in O.PARAM_KEYS})
-    eng3.enable_fused_ddp()
-    flat = idx.reshape(-1).cpu().numpy()
-    n = idx.shape[0]
-    hx = torch.from_numpy(im.reshape(-1, 784)[flat]).reshape(n, 64, 784).contiguous().pin_memory()
-    hy = torch.from_numpy(lb[flat]).reshape(n, 64).contiguous().pin_memory()
-    hl = torch.full((n,), -1.0).pin_memory()
-    eng3.train_steps_host(hx, hy, 64, n, masks=masks.contiguous(), host_loss_steps=hl, slots=8)
-    torch.cuda.synchronize()
-    eng3.check_comm()
-    eng3.check_feed()
-    if os.environ.get("DDPM_NO_ACT_EXCHANGE"):                 # same exchange as eng2 then: bit-identical
-        assert torch.equal(eng3.params, p20), "host-fed fused loop differs from the resident fused loop"
-        assert np.array_equal(hl.numpy(), l2)
-    rel3 = float((eng3.params - p20).abs().max() / p20.abs().max())
-    assert rel3 < 1e-4, ("host-fed fused vs resident fused", rel3)
-    assert np.abs(hl.numpy() - ref).max() < 1e-4 * np.abs(ref).max()
-    mine = eng3.params.clone()
-    other = mine.clone()
-    dist.broadcast(other, src=0)
-    assert torch.equal(mine, other), "host-fed fused replicas diverged"
-    dist.barrier()
     # ---- BASELINE.json's ConvNet (not in the reference; oracle = restatement): bucket all-reduce over NCCL.
     # Each rank's gradient of its own 16-sample batch, pre-divided by ws and summed, must equal the gradient of the
     # mean loss over the global batch (the restatement evaluated on all ws x 16 samples), and replicas must agree.
@@ -154,9 +153,10 @@ def main():
     assert torch.equal(mine, other), "convnet replicas diverged"
     dist.barrier()
     if rank == 0:
-        print("MULTIGPU_OK world %d exchange %s act_exchange %s max loss err %.2e fused-vs-nccl %.2e" %
-              (world, os.environ.get("DDPM_EXCHANGE", "default"), "off" if os.environ.get("DDPM_NO_ACT_EXCHANGE") else "on",
-               err, rel))
+        import json
+        print("PARITY_GATE " + json.dumps(rec))
+        print("MULTIGPU_OK world %d max loss err vs reference %s ddp-wrapped model err %s" %
+              (world, rec["max_loss_err"], ddp_err))
     dist.destroy_process_group()
 
 

@@ -478,6 +478,39 @@ def test_tf32_tensor_core_fc1_matches_fp32_path(ops, dev, data, golden, batch):
     assert not np.array_equal(lg, out[False][0])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch", [8192, 9000])
+def test_tf32_backward_stays_inside_workspace_beyond_batch_7168(ops, dev, data, golden, batch):
+    """dw1_tc_kernel writes one gradient slice per 224 rows (37 at batch 8192) while grads_kernel's own slicing is
+    capped at 32: the workspace must be sized for the larger count.  A guard region right behind the workspace must
+    stay untouched and the gradient must agree with the FFMA path."""
+    from pytorch_ddp_mnist_b200 import _lib
+    g = golden["traj_ws1"]
+    images, labels, im, lb = data
+    rng = np.random.default_rng(batch)
+    idx = torch.from_numpy(rng.integers(0, 60000, batch).astype(np.int64)).to(dev)
+    mask = torch.from_numpy((rng.random((batch, 128)) < 0.8).astype(np.uint8)).to(dev)
+    params = _flat(_params(g, "paramsN"), dev)
+    ws = ops.Workspace(batch, dev)
+    nbytes, guard = ws.nbytes, 8 << 20
+    big = torch.full((nbytes + guard,), 0xA5, dtype=torch.uint8, device=dev)
+    assert big.data_ptr() % 256 == 0
+    ws.buf = big[:nbytes]
+    _lib.check(_lib.lib.ddpm_workspace_init(_lib.ptr(ws.buf), batch, _lib.cur_stream()))
+    out = {}
+    for tf32 in (True, False):
+        loss = torch.zeros(2, device=dev)
+        grads = torch.zeros(O.N_PARAMS, device=dev)
+        ops.step_forward(params, ws, batch, images=images, labels=labels, idx=idx, mask=mask, prep_backward=True,
+                         loss=loss, tf32=tf32)
+        ops.step_backward(params, ws, batch, images=images, idx=idx, grads=grads, tf32=tf32)
+        torch.cuda.synchronize()
+        out[tf32] = grads.cpu().numpy()
+        assert bool((big[nbytes:] == 0xA5).all()), f"tf32={tf32}: wrote past the end of the workspace"
+    assert np.isfinite(out[True]).all()
+    assert _fro(out[True], out[False]) < 2e-2
+
+
 # ------------------------------------------------------------------------------------------
 # host-fed loop: batches stream from pinned host memory into a device ring while the kernel runs
 # ------------------------------------------------------------------------------------------
