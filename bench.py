@@ -543,7 +543,7 @@ def _context_numbers(torch, ops, eng, dev, B, world, dist, rank):
         if eng.comm is not None:
             try:
                 n = 200
-                ms = timed(lambda: ops.exchange_only(eng.comm, eng.ws, n), 3, warm=1) / n
+                ms = timed(lambda: ops.exchange_only(eng.comm, n), 3, warm=1) / n
                 out["fused_exchange_only_us"] = 1e3 * ms
                 out["fused_exchange_bus_gbs"] = 473_088 / (ms * 1e-3) * 2 * (world - 1) / world / 1e9
                 out["fused_exchange_note"] = ("the step kernel's gradient exchange alone: every CTA exchanges its share of "

@@ -79,6 +79,10 @@ int ddpm_dropout_mask_philox(uint8_t* d_mask, int batch, uint64_t seed, uint64_t
  * ddpm_step_forward on the same workspace left.  One workspace serves one stream at a time. */
 size_t ddpm_workspace_bytes(int max_batch);
 int    ddpm_workspace_init(void* d_workspace, int max_batch, void* stream);
+/* The leading part of a workspace that ddpm_step_forward / ddpm_step_backward use (control block + plain arrays); the
+ * rest of ddpm_workspace_bytes() holds the persistent kernel's tagged dataflow words.  ddpm_step_forward_static_scratch's
+ * built-in array is this many bytes for its row limit. */
+size_t ddpm_workspace_forward_bytes(int max_batch);
 
 #define DDPM_FWD_PREP_BACKWARD 1u  /* also compute dL/dz2, dL/dz1 from the CE gradient (training) */
 #define DDPM_FWD_PHILOX_MASK   2u  /* draw the dropout mask in-kernel (seed, step); d_mask unused */
@@ -148,6 +152,11 @@ int ddpm_train_steps_persistent(float* d_params, float* d_grads,
  * step kernel's launch shape (148 blocks x 256 threads, same dynamic shared memory) on `stream`.  bench.py times
  * it as the launch floor that SURVEY.md §8(d) asks to be reported beside the step time. */
 int ddpm_persist_launch_floor(int nlaunches, void* stream);
+/* Dataflow time-out flag of a workspace (no counterpart in the reference): the persistent kernel passes data between
+ * its phases as tagged words and waits for them with a ~3 s bound; a wait that gave up sets a sticky flag in the
+ * workspace's control block (and every later wait gives up at once, so a lost producer cannot hold the GPU).
+ * *h_err != 0 means the results of the launches since ddpm_workspace_init are not to be trusted.  Blocking (D2H). */
+int ddpm_workspace_error(const void* d_workspace, int* h_err);
 
 /* -------------------------------------------------------------------------------- fused data-parallel step
  * DistributedDataParallel's gradient averaging (mp:439: one 473,088-byte bucket, pre-divided by
@@ -184,6 +193,12 @@ void ddpm_comm_destroy(ddpm_comm* c);
  *              traffic), fc1's gradient (85 % of the bucket) is not exchanged at all: ranks
  *              exchange their dz1 rows (32 KB) and each forms the global-batch dW1 tile itself from the
  *              resident dataset — same sums in the same (rank) order on every rank. */
+/* Measurement / test aid (no counterpart in the reference): the gradient exchange of the fused step ALONE - the same
+ * threads exchange the same elements of the 473,088-byte bucket as in ddpm_train_steps_fused_ddp, `nsteps` times, with
+ * no forward/backward work.  Rank r contributes (r + 1) * (1 + (e & 1023)) / 1024 + (step & 255) to element e; with
+ * d_out != NULL (f32[118272], 16-byte aligned) the reduced values of the last step are stored there.  Collective:
+ * every rank calls it with the same nsteps. */
+int ddpm_comm_exchange_only(ddpm_comm* comm, int nsteps, float* d_out, void* stream);
 int ddpm_train_steps_fused_ddp(ddpm_comm* comm, float* d_params,
                                const uint8_t* d_images, const uint8_t* d_labels, int64_t n_samples,
                                const int64_t* d_idx, const int64_t* d_idx_all, int64_t idx_stride,

@@ -11,7 +11,8 @@ import os
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libddpmnist_b200.so")
+# DDPM_LIB: another build of the same library (kernel experiments: scripts build variants next to the default one)
+LIB_PATH = os.environ.get("DDPM_LIB") or os.path.join(_HERE, "libddpmnist_b200.so")
 
 IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
@@ -21,7 +22,7 @@ CN_BWD_TRAIN, CN_BWD_TF32, CN_BWD_FWD_WAS_TF32 = 1, 2, 4
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512
 CN_N_PARAMS, CN_MAX_BATCH = 1199882, 8192
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class DDPMError(RuntimeError):
@@ -49,6 +50,7 @@ SIGNATURES = {
     "ddpm_dropout_mask_philox": (_i32, [_vp, _i32, _u64, _u64, _vp]),
     "ddpm_workspace_bytes": (C.c_size_t, [_i32]),
     "ddpm_workspace_init": (_i32, [_vp, _i32, _vp]),
+    "ddpm_workspace_forward_bytes": (C.c_size_t, [_i32]),
     "ddpm_step_forward": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _u64, _u64, _i32, _u32,
                                  _vp, _vp, _vp, _vp]),
     "ddpm_step_forward_static_scratch": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _u64, _u64, _i32,
@@ -56,6 +58,8 @@ SIGNATURES = {
     "ddpm_train_steps_persistent": (_i32, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _u64, _u64, _i32, _i32, _u32,
                                            _f32, _f32, _vp, _vp, _vp, _vp]),
     "ddpm_persist_launch_floor": (_i32, [_i32, _vp]),
+    "ddpm_workspace_error": (_i32, [_vp, C.POINTER(_i32)]),
+    "ddpm_comm_exchange_only": (_i32, [_vp, _i32, _vp, _vp]),
     "ddpm_comm_create": (_i32, [_i32, _i32, C.POINTER(_vp)]),
     "ddpm_comm_ipc_handle": (_i32, [_vp, _vp]),
     "ddpm_comm_connect": (_i32, [_vp, _vp]),

@@ -2,7 +2,7 @@
 # Builds libddpmnist_b200.so in-tree for sm_100a (cross-compiles without a GPU).
 set -euo pipefail
 HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
-OUT="${HERE}/../libddpmnist_b200.so"
+OUT="${DDPM_OUT:-${HERE}/../libddpmnist_b200.so}"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "${NVCC}" -shared -Xcompiler -fPIC -O3 -std=c++17 -lineinfo \
     -gencode arch=compute_100a,code=sm_100a \

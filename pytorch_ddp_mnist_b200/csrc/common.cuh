@@ -87,8 +87,25 @@ struct WsLayout {
     size_t rowloss;   // f32 [B]
     size_t yb;        // u8  [B]
     size_t gpart;     // f32 [bsplit][NP] partial gradients of the batch slices (batch >= 1024 only)
+    size_t fend;      // end of the plain (float / byte) arrays above
+    // persistent kernel only (batch <= PERSIST_MAX_BATCH): dataflow buffers of 8-byte (fp32 value, 32-bit step tag)
+    // words, double-buffered by step parity.  The region starts at the SAME offset for every batch <= 512 (right
+    // behind the plain arrays of a 512-row layout) and is zeroed by ddpm_workspace_init, so that no plain array of
+    // any layout ever aliases a tagged word.
+    size_t ll;        // start of the region
+    size_t ll_part;   // u64 [2][14 pixel tiles][B][128]  fc1 partial products
+    size_t ll_act;    // u64 [2][B][LL_ACT_WORDS]         per-row dz1 | dz2 | h1d | h2 | dz3
+    size_t ll_loss;   // u64 [2][B]                       per-row loss
+    size_t ll_b1;     // u64 [2][128]                     fc1 bias after the update (read by the next step's rows)
+    size_t ll_bytes;
     size_t total;
 };
+constexpr int PERSIST_MAX_BATCH = 512;
+constexpr int LL_ACT_WORDS = 528;       // dz1 128 | dz2 128 | h1d 128 | h2 128 | dz3 16
+// control words (u32 index into the 256-byte ctrl block at the start of the workspace)
+//   0 ticket (rows kernels)   1 train flag   4,5 finished-CTA counter (u64)   6,7 'parameters ready' counter (u64)
+//   8,9 steps run so far by the persistent kernel on this workspace (u64: the tag base)   12 dataflow timeout flag
+constexpr int CTRL_FIN64 = 2, CTRL_READY64 = 3, CTRL_EPOCH64 = 4, CTRL_ERR32 = 12;
 int fc1_ksplit(int batch);              // how many K splits G1 uses for this batch
 int grads_bsplit(int batch);            // how many batch slices grads_kernel uses
 size_t part1_rows_capacity(int max_batch);

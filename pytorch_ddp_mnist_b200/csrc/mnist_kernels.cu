@@ -70,13 +70,11 @@ WsLayout ws_layout(int max_batch) {
     return L;
 }
 
-static WsLayout ws_layout_compute(int max_batch) {
-    WsLayout L;
-    size_t off = 0;
+// plain arrays of a `max_batch`-row layout, starting at byte `off`; returns their end
+static size_t lay_plain(WsLayout& L, size_t off, int max_batch) {
     const size_t B = (size_t)max_batch;
-    L.ctrl = off;    off = al256(off + 64 * sizeof(uint32_t));
     size_t part_rows = part1_rows_capacity(max_batch);
-    if (part_rows < (size_t)14 * B) part_rows = (size_t)14 * B;      // persistent kernel: 14 pixel-tile partials
+    if (part_rows < (size_t)14 * B) part_rows = (size_t)14 * B;      // (v2 persistent kernel: 14 pixel-tile partials)
     L.part1 = off;   off = al256(off + part_rows * HID * sizeof(float));
     L.h1d = off;     off = al256(off + B * HID * sizeof(float));
     L.h2 = off;      off = al256(off + B * HID * sizeof(float));
@@ -92,7 +90,35 @@ static WsLayout ws_layout_compute(int max_batch) {
     int gslices = grads_bsplit(max_batch) > 1 ? grads_bsplit(max_batch) : 0;
     if (max_batch >= 2048 && dw1_tc_slices(max_batch) > gslices) gslices = dw1_tc_slices(max_batch);
     L.gpart = off;   off = al256(off + (size_t)gslices * NP * sizeof(float));
-    L.total = off;
+    return off;
+}
+
+static size_t lay_ll(WsLayout& L, size_t off, int batch) {
+    const size_t B = (size_t)batch;
+    L.ll = off;
+    L.ll_part = off; off = al256(off + 2 * 14 * B * HID * sizeof(unsigned long long));
+    L.ll_act = off;  off = al256(off + 2 * B * LL_ACT_WORDS * sizeof(unsigned long long));
+    L.ll_loss = off; off = al256(off + 2 * B * sizeof(unsigned long long));
+    L.ll_b1 = off;   off = al256(off + 2 * HID * sizeof(unsigned long long));
+    L.ll_bytes = off - L.ll;
+    return off;
+}
+
+static WsLayout ws_layout_compute(int max_batch) {
+    WsLayout L;
+    memset(&L, 0, sizeof(L));
+    L.ctrl = 0;
+    const size_t first = al256(64 * sizeof(uint32_t));
+    WsLayout cap;
+    const size_t plain_end_512 = lay_plain(cap, first, PERSIST_MAX_BATCH);
+    if (max_batch <= PERSIST_MAX_BATCH) {
+        L.fend = lay_plain(L, first, max_batch);               // <= plain_end_512: every size grows with the batch
+        L.total = lay_ll(L, plain_end_512, max_batch);
+    } else {                                                   // the persistent kernel never runs at this batch, but a
+        const size_t ll_end = lay_ll(L, plain_end_512, PERSIST_MAX_BATCH);   // smaller one may on the same workspace
+        L.fend = lay_plain(L, ll_end, max_batch);
+        L.total = L.fend;
+    }
     return L;
 }
 
@@ -1084,7 +1110,7 @@ extern "C" {
 
 const char* ddpm_last_error(void) { return g_err; }
 
-int ddpm_abi_version(void) { return 5; }
+int ddpm_abi_version(void) { return 6; }
 
 int ddpm_decode_lut_host(float* h_lut256) {
     DDPM_CHECK_ARG(h_lut256 != nullptr, "ddpm_decode_lut_host: null output");
@@ -1123,10 +1149,19 @@ size_t ddpm_workspace_bytes(int max_batch) {
     return ws_layout(max_batch).total;
 }
 
+size_t ddpm_workspace_forward_bytes(int max_batch) {
+    if (max_batch <= 0) return 0;
+    return ws_layout(max_batch).fend;
+}
+
 int ddpm_workspace_init(void* d_workspace, int max_batch, void* stream) {
     DDPM_CHECK_ARG(d_workspace != nullptr && max_batch > 0, "ddpm_workspace_init: bad arguments");
     DDPM_CHECK_ARG(((uintptr_t)d_workspace & 255) == 0, "ddpm_workspace_init: workspace must be 256-byte aligned");
     DDPM_CUDA(cudaMemsetAsync(d_workspace, 0, 64 * sizeof(uint32_t), (cudaStream_t)stream));
+    // the persistent kernel's dataflow words carry step tags that only ever grow on one workspace; memory handed
+    // out by a caching allocator may hold the tagged words of an earlier workspace: start from tag 0 everywhere
+    const WsLayout L = ws_layout(max_batch);
+    DDPM_CUDA(cudaMemsetAsync((char*)d_workspace + L.ll, 0, L.ll_bytes, (cudaStream_t)stream));
     return 0;
 }
 
@@ -1269,7 +1304,7 @@ int ddpm_sgd_step(float* d_params, const float* d_grads, int64_t n, float lr, fl
 // pointer is what the kernels receive.
 namespace ddpm {
 
-constexpr size_t STATIC_SCRATCH_BYTES = 3490816;   // == ddpm_workspace_bytes(DDPM_STATIC_SCRATCH_MAX_BATCH)
+constexpr size_t STATIC_SCRATCH_BYTES = 3490816;   // the forward's arrays of a DDPM_STATIC_SCRATCH_MAX_BATCH-row workspace layout
 static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
 
 static void* g_static_scratch_ptr[64] = {};        // per device, filled on first use
@@ -1303,7 +1338,7 @@ extern "C" int ddpm_step_forward_static_scratch(
     DDPM_CHECK_ARG((flags & DDPM_FWD_PREP_BACKWARD) == 0,
                    "ddpm_step_forward_static_scratch: forward/eval only (DDPM_FWD_PREP_BACKWARD needs a "
                    "caller-owned workspace that ddpm_step_backward can read)");
-    DDPM_CHECK_ARG(ws_layout(batch).total <= STATIC_SCRATCH_BYTES,
+    DDPM_CHECK_ARG(ws_layout(batch).fend <= STATIC_SCRATCH_BYTES,
                    "ddpm_step_forward_static_scratch: internal scratch too small for batch %d", batch);
     void* scratch = nullptr;
     if (static_scratch_for_current_device(&scratch)) return 1;

@@ -1,33 +1,38 @@
-// Persistent, weight-stationary training kernel (v2) — one cooperative launch runs `nsteps`
-// optimisation steps of the MNIST MLP at a small per-rank batch (the launch/latency-bound regime).
+// Persistent, weight-stationary training kernel — one cooperative launch runs `nsteps` optimisation steps
+// of the MNIST MLP at a small per-rank batch (the launch/latency-bound regime).
 //
-// Why: at batch 64 a step moves 2.5 MB and does 32 MFLOP (0.4 us of HBM time); three separate
-// kernels spend their time in launch gaps and dependent global round trips (profiles/r01_v1_*).
-// Here the grid stays resident, the phases of a step are separated by two grid barriers, and
-// the 401 KB fc1 weight matrix never leaves the chip: CTA c < 112 OWNS the W1 tile
-// [16 hidden units x 56 pixels], keeps it in shared memory across steps, computes that tile's
-// contribution to z1 (phase A) and that tile's gradient (phase C) from the same decoded pixel
-// tile, and applies the SGD update in place.  No other CTA ever needs W1, so nothing orders
-// phase C of step t against phase A of step t+1.
+// Why: at batch 64 a step moves 2.5 MB and does 32 MFLOP (0.4 us of HBM time); separate kernels spend their
+// time in launch gaps and dependent global round trips (profiles/r01_v1_*).  Here the grid stays resident and
+// the 401 KB fc1 weight matrix never leaves the chip: CTA c < 112 OWNS the W1 tile [16 hidden units x 56
+// pixels], keeps it in shared memory across steps, computes that tile's contribution to z1 (phase A) and that
+// tile's gradient (phase C) from the same decoded pixel tile, and applies the SGD update in place.
 //
 //   phase A  (CTAs 0..111)      part[nt][b][16 units] = X[b][56 px of tile nt] . W1tile^T
-//   -- grid barrier --
-//   phase B  (CTA r -> rows r, r+G, ..)  z1 = sum of 14 partials + b1 -> ReLU -> dropout -> fc2
-//            -> ReLU -> fc3 -> log-softmax/NLL -> dlogits -> dz2 -> dz1   (W2 re-staged per step
-//            with cp.async into an XOR-swizzled layout: conflict-free by row and by column)
-//   -- grid barrier --
-//   phase C  CTAs 0..111: dW1 tile (+SGD in smem, + bucket);  112..119: dW2 tiles;  120: dW3;
-//            121: db1, db2;  122: batch loss (fixed-order sum)
+//   phase B  (CTA r -> rows r, r+148, ..)  z1 = sum of 14 partials + b1 -> ReLU -> dropout -> fc2 -> ReLU -> fc3
+//            -> log-softmax/NLL -> dlogits -> dz2 -> dz1   (W2 in registers, W3 / biases in shared memory)
+//   phase C  CTAs 0..111: dW1 tile (+ SGD in smem);  112..143: dW2 tiles, db2;  144..147: dW3 tiles, batch loss
+//
+// Round 2: NO grid barrier between the phases.  Everything one phase hands to the next travels as 8-byte
+// (fp32 value, 32-bit step tag) words in L2 - the "flag in the data" protocol the cross-GPU exchange already used:
+// the producer stores the word, the consumer polls the very word it needs until the tag is this step's.  A grid
+// barrier cost 3,800 cycles between A and B and 2,600 between B and C (release fence behind the CTA's stores +
+// atomic + poll, profiles/r02_*timeline*); a tagged word is visible one L2 hop after it was stored.  Buffers are
+// double-buffered by step parity: a producer can reach step t+2 only after every consumer of step t has finished
+// with it (each phase needs the output of ALL CTAs of the phase before).  Updated W2 / W3 / biases are published
+// through one monotonic counter (release by the 44 updating CTAs, polled by the row CTAs).
 //
 // Every sum has a fixed order: results are bit-identical run to run and independent of timing.
-#include <cooperative_groups.h>
 #include <cuda_pipeline.h>
 #include <stdlib.h>
 
 #include "common.cuh"
 
-#ifndef DDPM_POLL_SLEEP
-#define DDPM_POLL_SLEEP 0
+#ifndef DDPM_POLL_BACKOFF_NS
+#define DDPM_POLL_BACKOFF_NS 0           // sleep between polls of a word that has not arrived (0 = spin).  Measured with
+                                         // %globaltimer stamps (scripts/persist_timeline_abs.py): with __nanosleep(64) a CTA
+                                         // that had been waiting for a while saw a word 1.3 - 2.3 us after it was stored,
+                                         // a CTA that had just started polling after 0.58 us; spinning pollers do not slow
+                                         // the L2 down measurably (scripts/micro/bcast_bench.cu)
 #endif
 
 namespace ddpm {
@@ -41,13 +46,14 @@ constexpr int N_W3T = 4;                              // dW3 column tiles (32 co
 constexpr int CTA_W2 = N_W1, CTA_W3 = N_W1 + N_W2T;
 constexpr int P_GRID = CTA_W3 + N_W3T;                // 148 = one CTA per SM
 constexpr int N_SMALL = N_W2T + N_W3T;                // 36 CTAs update W2, W3, b2
-constexpr int N_READY = N_SMALL + N_W1 / N_NT;        // ... plus the 8 W1 CTAs (pixel tile 0) that update b1: bumps of the 'ready' counter per step
+constexpr int N_READY = N_SMALL;                      // bumps of the 'ready' counter per step (b1 travels as tagged words)
 constexpr int CR = 64;                                // batch rows per smem chunk
 constexpr int XS_LD = 60;                             // padded row of the decoded pixel tile (16B aligned)
-constexpr int PERSIST_MAX_BATCH = 512;
+constexpr int W1_ACTIVE = 4 * 4 * (NT / 4);           // 224 threads hold the 16 x 56 gradient tile (4 values each)
 #define DDPM_MAX_WORLD 8
-// activation exchange: per (parity, source rank, batch row) 528 eight-byte words
-constexpr int ACT_DZ1 = 0, ACT_DZ2 = 128, ACT_H1D = 256, ACT_H2 = 384, ACT_DZ3 = 512, ACT_ROW_WORDS = 528;
+constexpr int ACT_DZ1 = 0, ACT_DZ2 = 128, ACT_H1D = 256, ACT_H2 = 384, ACT_DZ3 = 512;   // words of a row in ll_act
+constexpr int XACT_ROW_WORDS = HID;                   // cross-GPU dz1 exchange: 128 words per (parity, source rank, row)
+constexpr long long POLL_TIMEOUT_CYCLES = 6000000000LL;   // ~3 s
 
 struct PersistArgs {
     float* params; float* grads;
@@ -56,8 +62,13 @@ struct PersistArgs {
     uint64_t seed, step0;
     int B, nsteps; float gscale, lr; int train;
     float* loss2; float* loss_steps;
-    float* part; float* h1d; float* h2; float* dz2; float* dz1; float* dz3; float* rowloss;
-    unsigned long long* bar;                          // [0] monotonic arrival counter, [1] monotonic 'W2/W3/b ready' counter
+    unsigned long long* llpart;                       // [2][14][B][128] tagged fc1 partial products
+    unsigned long long* llact;                        // [2][B][LL_ACT_WORDS] tagged per-row activations / gradients
+    unsigned long long* llloss;                       // [2][B] tagged per-row losses
+    unsigned long long* llb1;                         // [2][128] tagged fc1 bias of the NEXT step (its producers get their
+                                                      // input last, so it does not travel with the 'ready' counter)
+    unsigned long long* ctl;                          // the workspace's control block as u64 words (CTRL_*64)
+    int* lerr;                                        // dataflow timeout flag (ctrl word CTRL_ERR32)
     long long* dbg;                                   // optional [grid][8 steps][16] clock64 stamps (profiling aid)
     // ---- fused data-parallel mode (world > 1): gradient tiles are exchanged over NVLink peer memory
     int world, rank, two_stage;
@@ -65,13 +76,13 @@ struct PersistArgs {
     unsigned long long* xrecv[DDPM_MAX_WORLD];        // every rank's receive buffer [2 parities][world sources][NP] of
                                                       // 8-byte (value, step) words, peer-mapped
     int* xerr;                                        // local error word (exchange timeout)
-    // activation exchange (batch <= 64): instead of the 473 KB of gradients, ranks exchange the per-row quantities
-    // the gradients are made of (dz1, dz2, h1d, h2: 128 each, dz3: 16 -> 135 KB per rank) as they are produced in
-    // phase B, and every rank forms the GLOBAL-batch gradient tiles itself, summing sources in rank order (all
-    // ranks hold the whole dataset and know every shard).  Nothing is exchanged after phase C any more.
-    unsigned long long* xrecv_dz[DDPM_MAX_WORLD];     // every rank's buffer [2 parities][world sources][CR rows][ACT_ROW_WORDS]
+    // dz1 exchange (batch <= 64): instead of fc1's 401 KB gradient, ranks exchange their dz1 rows (32 KB) as they are
+    // produced in phase B, and every rank forms the GLOBAL-batch dW1 tiles itself, summing sources in rank order
+    // (all ranks hold the whole dataset and know every shard)
+    unsigned long long* xrecv_dz[DDPM_MAX_WORLD];     // every rank's buffer [2 parities][world sources][CR rows][XACT_ROW_WORDS]
     const int64_t* idx_all; size_t idx_stride;        // i64 [world][idx_stride]: every rank's batches of this launch
     int act_exchange;
+    float* xout;                                      // exchange-only kernel: reduced values of the last step (or NULL)
     // ---- host-fed mode: the batches of this launch arrive in a device ring while the kernel runs; step s may read
     // its slot once feed_flags[(feed_g0 + s) % feed_slots] == feed_g0 + s + 1
     const unsigned long long* feed_flags; unsigned long long feed_g0; int feed_slots; int* feed_err;
@@ -83,12 +94,13 @@ struct __align__(16) PersistSmem {
     float b1[HID], b2[HID];
     float w1t[NT * MT];                               // [n][m]  owned W1 tile (persistent across steps)
     float xs[2][CR * XS_LD];                          // decoded pixels of the tile, [row][60]; double buffered
-    float xsx[CR * XS_LD];                            // pixel tile of another rank's batch (activation exchange)
+    float xsx[CR * XS_LD];                            // pixel tile of another rank's batch (dz1 exchange)
     float dzt[CR * MT];                               // dz1 tile [row][16]
     float hs[HID], h2s[HID], ds[HID];                 // row vectors
     float red[2 * HID];
-    float zs[NCP], dzs[NCP];
+    float zs[NCP];
     int ylab;
+    unsigned long long epoch0, ready_base;
     float lut[256];
 };
 
@@ -97,37 +109,29 @@ __device__ __forceinline__ unsigned long long ld_acquire64(const unsigned long l
     asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void red_release64(unsigned long long* p) {
-    asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(p) : "memory");
-}
-
-// Grid barrier on ONE monotonic 64-bit counter (all CTAs are co-resident: cooperative launch).
-// Arrive = one fire-and-forget release reduction (the bar.sync before it makes the CTA's writes
-// visible to thread 0; release is cumulative); wait = acquire-poll until the counter reaches this
-// barrier's target.  Every barrier adds exactly gridDim.x, so the value a CTA reads at kernel
-// start, rounded down to a multiple of gridDim.x, is the launch's base (at most gridDim.x-1
-// arrivals can precede its own): no reset, no second atomic, no host-side zeroing per launch.
-constexpr int BAR_TID = P_THREADS - 1;     // the barrier thread: it issues no global loads/stores of its own before
-                                           // arriving, so the release fence has nothing of its own to wait for
 __device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void grid_arrive(unsigned long long* ctr, unsigned long long& target) {
-    __syncthreads();
-    if (threadIdx.x == BAR_TID) { target += gridDim.x; red_release64(ctr); }
+__device__ __forceinline__ void red_release64(unsigned long long* p) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], 1;" :: "l"(p) : "memory");
 }
-__device__ __forceinline__ void grid_wait(unsigned long long* ctr, const unsigned long long& target) {
-    // acquire-poll: measured 2461 cycles per barrier on B200 (148 CTAs) against 2823 for a relaxed poll
-    // followed by fence.acq_rel, 2420 for cooperative_groups grid.sync() and 1571 with no ordering at
-    // all (scripts/micro/barrier_bench.cu)
-    if (threadIdx.x == BAR_TID) { while (ld_acquire64(ctr) < target) { } }
-    __syncthreads();
-}
-__device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned long long& target) {
-    grid_arrive(ctr, target);
-    grid_wait(ctr, target);
+
+// Called when a polled word has not arrived yet.  Backs off a little (a whole grid polling L2 flat out slows the
+// producers down), and every 16th miss looks at the clock and at the error word: a wait gives up after ~3 s, and
+// once ANY wait has given up every later one gives up within microseconds (the error word is sticky), so a dead
+// peer or a lost producer can never hold the non-preemptible grid for more than a few seconds in total.
+__device__ __forceinline__ bool poll_miss(int* err, long long t0, unsigned& spins) {
+    ++spins;
+#if DDPM_POLL_BACKOFF_NS > 0
+    if (spins > 2) __nanosleep(spins > 6 ? DDPM_POLL_BACKOFF_NS : DDPM_POLL_BACKOFF_NS / 2);
+#endif
+    if ((spins & 15u) == 0u) {
+        if (*(volatile int*)err != 0) return true;
+        if (clock64() - t0 > POLL_TIMEOUT_CYCLES) { *err = 1; return true; }
+    }
+    return false;
 }
 
 // host-fed mode: slot of step `step` filled?  The copy stream carries pixels, labels and then a stream memory
@@ -147,14 +151,14 @@ __device__ __forceinline__ void feed_wait(const PersistArgs& a, int step) {
     if (*(volatile int*)a.feed_err) return;                                // already timed out once: do not wait again
     const long long t0 = clock64();
     while (!feed_ready(a, step))
-        if (clock64() - t0 > 6000000000LL) { *a.feed_err = 1; break; }     // ~3 s: the host stopped feeding
+        if (clock64() - t0 > POLL_TIMEOUT_CYCLES) { *a.feed_err = 1; break; }     // ~3 s: the host stopped feeding
 }
 
 __device__ __forceinline__ int w1_idx(int m, int n) { return (((n >> 2) * MT + m) << 2) + (n & 3); }   // [n/4][m][n%4]
 
 // Pixel tile [rows c0..c0+CR) x [56 pixels of tile nt]: loads first (all index loads, then all
 // pixel loads: two dependent round trips in total), LUT decode + store to smem later, so the
-// latency can sit behind a barrier wait.
+// latency can sit behind the wait for the next phase's operands.
 constexpr int PX_PER_ROW = NT / 4;                                         // 14 words of 4 pixels
 constexpr int PX_ITERS = (CR * PX_PER_ROW + P_THREADS - 1) / P_THREADS;    // 4
 struct PixelRegs { int64_t sidx[PX_ITERS]; uint32_t v[PX_ITERS]; unsigned ok; };
@@ -219,13 +223,10 @@ __device__ __forceinline__ void grad_out(float* gout, float lr, float* params, i
     if (lr != 0.f) params[off] = fmaf(-lr, g, pold);
 }
 
-// ---- fused data-parallel exchange: low-latency "flag in the data" protocol over NVLink peer memory.
-// Every gradient value travels as one 8-byte word (fp32 value, 32-bit step number) stored straight
-// into the receive buffer of each peer; 8-byte stores are single transactions, so a word whose
-// step field equals T carries step T's value.  No fences, no separate flags, no barrier: the thread
-// that produced an element sends it and later polls the same element of every source in its own
-// (local) receive buffer, summing in rank order — identical on all ranks, hence bit-identical
-// replicas.  Slots are double-buffered by step parity: a rank can only be one step ahead of a peer.
+// ---- tagged words ("flag in the data"): every value travels as one 8-byte word (fp32 value, 32-bit step tag).
+// 8-byte stores are single transactions, so a word whose tag equals T carries step T's value: no fences, no
+// separate flags.  Used inside the GPU (phase A -> B -> C, through L2) and between GPUs (gradient exchange, straight
+// into the peer's receive buffer over NVLink).
 template <int N>
 __device__ __forceinline__ void ll_store(unsigned long long* dst, unsigned t32, const float (&v)[N]) {
     if (N == 1) {
@@ -237,121 +238,115 @@ __device__ __forceinline__ void ll_store(unsigned long long* dst, unsigned t32, 
                          "r"(t32), "r"(__float_as_uint(v[i + (N > 1 ? 1 : 0)])), "r"(t32) : "memory");
     }
 }
+__device__ __forceinline__ void ll_store1(unsigned long long* dst, unsigned t32, float v) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"(__float_as_uint(v)), "r"(t32) : "memory");
+}
 template <int N>
-__device__ __forceinline__ void ll_poll(const PersistArgs& a, const unsigned long long* src, unsigned t32, long long t0,
+__device__ __forceinline__ void ll_poll(int* err, const unsigned long long* src, unsigned t32, long long t0,
                                         float (&got)[N]) {
+    unsigned spins = 0;
     if (N == 1) {
         unsigned x, f;
-        do {
+        for (;;) {
             asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
-            if (f != t32 && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }              // ~3 s: peer missing
-        } while (f != t32);
+            if (f == t32 || poll_miss(err, t0, spins)) break;
+        }
         got[0] = __uint_as_float(x);
     } else {
 #pragma unroll
         for (int i = 0; i < N; i += 2) {
             unsigned x0, f0, x1, f1;
-            do {
+            for (;;) {
                 asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(f0), "=r"(x1), "=r"(f1)
                              : "l"(src + i) : "memory");
-                if ((f0 != t32 || f1 != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
-            } while (f0 != t32 || f1 != t32);
+                if ((f0 == t32 && f1 == t32) || poll_miss(err, t0, spins)) break;
+            }
             got[i] = __uint_as_float(x0); got[i + (N > 1 ? 1 : 0)] = __uint_as_float(x1);
         }
     }
 }
-// v: this rank's contribution on entry, the sum over all ranks (rank order) on exit.
+// Cross-GPU all-reduce of this thread's N gradient values.  v: this rank's contribution on entry, the sum over all
+// ranks (rank order) on exit.
 //   one-shot  (a.two_stage == 0): everyone pushes to everyone, everyone sums: 1 NVLink hop, (ws-1) x bytes
-//   two-stage (a.two_stage == 1): the elements of CTA `cta` have a home rank cta % ws; the others push their
-//             contribution to the home, the home sums and pushes the result back: 2 hops, 2(ws-1)/ws x bytes
+//   two-stage (a.two_stage == 1): the values of this THREAD have a home rank `home`; the others push their
+//             contribution to the home, the home sums and pushes the result back: 2 hops, 2(ws-1)/ws x bytes.
+//             Homes are spread over the threads of every CTA (thread slices of a tile), so on every rank every SM
+//             sends and receives the same share (round 1 made whole CTAs home: 14 SMs per rank did all the summing).
+// All pushes of a thread come before any of its waits, so diverged lanes of a warp never wait for each other.
 template <int N>
-__device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int cta, int off, float (&v)[N]) {
+__device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
     const unsigned t32 = (unsigned)T;
     const size_t par = (size_t)(T & 1) * a.world;
     const long long t0 = clock64();
-    const int home = cta % a.world;
-    if (a.two_stage && a.rank != home) {
+    const bool is_home = !a.two_stage || home == a.rank;
+    if (!is_home) {
         ll_store<N>(a.xrecv[home] + (par + a.rank) * NP + off, t32, v);
-        ll_poll<N>(a, a.xrecv[a.rank] + (par + home) * NP + off, t32, t0, v);
-        return;
-    }
-    if (!a.two_stage) {
+    } else if (!a.two_stage) {
         for (int r = 0; r < a.world; ++r)
             if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
     }
-    // (polling every source at once before summing was tried: the extra live registers spill in the 255-register
-    //  kernel and the step got slower at 2 and 4 GPUs: 10.97 -> 8.94 M, 15.7 -> 13.3 M img/s)
-    float sum[N];
-    for (int r = 0; r < a.world; ++r) {
-        float got[N];
-        if (r == a.rank) {
+    if (is_home) {
+        // (polling every source at once before summing was tried: the extra live registers spill in the 255-register
+        //  kernel and the step got slower at 2 and 4 GPUs: 10.97 -> 8.94 M, 15.7 -> 13.3 M img/s)
+        float sum[N];
+        for (int r = 0; r < a.world; ++r) {
+            float got[N];
+            if (r == a.rank) {
 #pragma unroll
-            for (int i = 0; i < N; ++i) got[i] = v[i];
-        } else {
-            ll_poll<N>(a, a.xrecv[a.rank] + (par + r) * NP + off, t32, t0, got);
+                for (int i = 0; i < N; ++i) got[i] = v[i];
+            } else {
+                ll_poll<N>(a.xerr, a.xrecv[a.rank] + (par + r) * NP + off, t32, t0, got);
+            }
+#pragma unroll
+            for (int i = 0; i < N; ++i) sum[i] = (r == 0) ? got[i] : sum[i] + got[i];
+        }
+        if (a.two_stage) {
+            for (int r = 0; r < a.world; ++r)
+                if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
         }
 #pragma unroll
-        for (int i = 0; i < N; ++i) sum[i] = (r == 0) ? got[i] : sum[i] + got[i];
+        for (int i = 0; i < N; ++i) v[i] = sum[i];
+    } else {
+        ll_poll<N>(a.xerr, a.xrecv[a.rank] + (par + home) * NP + off, t32, t0, v);
     }
-    if (a.two_stage) {
-        for (int r = 0; r < a.world; ++r)
-            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
-    }
-#pragma unroll
-    for (int i = 0; i < N; ++i) v[i] = sum[i];
 }
 
-__device__ __forceinline__ void act_push(const PersistArgs& a, unsigned long long T, int row, int word, float v) {
-    const float one[1] = {v};
-    const size_t slot = (((size_t)(T & 1) * a.world + a.rank) * CR + row) * ACT_ROW_WORDS + word;
-    for (int r = 0; r < a.world; ++r)
-        if (r != a.rank) ll_store<1>(a.xrecv_dz[r] + slot, (unsigned)T, one);
-}
-// dst[r][0..NCOLS) for rows r < CR: from this rank's workspace (src_rank == a.rank) or from the words rank
-// `src_rank` pushed into this rank's buffer (polled until they carry step T); rows >= B are zero.
+// dst[r][0..NCOLS) for rows r < CR from tagged words at base[r * row_stride + c] (polled until they carry tag
+// t32); rows >= nrows are zero.  First round: every poll of this thread in flight at once; then re-poll only
+// what has not arrived.
 template <int NCOLS>
-__device__ __forceinline__ void act_stage(const PersistArgs& a, unsigned long long T, int src_rank, float* dst, int dst_ld,
-                                          const float* local, int local_ld, int col0, int word0) {
+__device__ __forceinline__ void ll_stage(const unsigned long long* base, size_t row_stride, int nrows, unsigned t32,
+                                         float* dst, int dst_ld, int* err) {
     constexpr int PAIRS = NCOLS / 2, PER_THREAD = CR * PAIRS / P_THREADS;      // 2 (16 columns) or 4 (32 columns)
     static_assert(CR * PAIRS % P_THREADS == 0, "tile must divide evenly");
-    const unsigned long long* base =
-        a.xrecv_dz[a.rank] + (((size_t)(T & 1) * a.world + src_rank) * CR) * ACT_ROW_WORDS + word0 + col0;
-    const unsigned t32 = (unsigned)T;
-    float2 v[PER_THREAD];
-    if (src_rank == a.rank) {
+    unsigned x0[PER_THREAD], f0[PER_THREAD], x1[PER_THREAD], f1[PER_THREAD];
+#pragma unroll
+    for (int i = 0; i < PER_THREAD; ++i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
+        x0[i] = x1[i] = 0u; f0[i] = f1[i] = t32;
+        if (r < nrows)
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0[i]), "=r"(f0[i]), "=r"(x1[i]), "=r"(f1[i])
+                         : "l"(base + (size_t)r * row_stride + c2) : "memory");
+    }
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    for (;;) {                                    // every round re-issues ALL loads that are still missing, together
+        bool missing = false;
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) missing |= (f0[i] != t32 || f1[i] != t32);
+        if (!missing || poll_miss(err, t0, spins)) break;
 #pragma unroll
         for (int i = 0; i < PER_THREAD; ++i) {
             const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
-            v[i] = r < a.B ? __ldcg(reinterpret_cast<const float2*>(local + (size_t)r * local_ld + col0 + c2))
-                           : make_float2(0.f, 0.f);
-        }
-    } else {
-        // first round: every poll of this thread in flight at once; then re-poll only what has not arrived
-        unsigned x0[PER_THREAD], f0[PER_THREAD], x1[PER_THREAD], f1[PER_THREAD];
-#pragma unroll
-        for (int i = 0; i < PER_THREAD; ++i) {
-            const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
-            x0[i] = x1[i] = 0u; f0[i] = f1[i] = t32;
-            if (r < a.B)
+            if (f0[i] != t32 || f1[i] != t32)
                 asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0[i]), "=r"(f0[i]), "=r"(x1[i]), "=r"(f1[i])
-                             : "l"(base + (size_t)r * ACT_ROW_WORDS + c2) : "memory");
-        }
-        const long long t0 = clock64();
-#pragma unroll
-        for (int i = 0; i < PER_THREAD; ++i) {
-            const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
-            while (f0[i] != t32 || f1[i] != t32) {
-                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0[i]), "=r"(f0[i]), "=r"(x1[i]), "=r"(f1[i])
-                             : "l"(base + (size_t)r * ACT_ROW_WORDS + c2) : "memory");
-                if ((f0[i] != t32 || f1[i] != t32) && clock64() - t0 > 6000000000LL) { *a.xerr = 1; break; }
-            }
-            v[i] = make_float2(__uint_as_float(x0[i]), __uint_as_float(x1[i]));
+                             : "l"(base + (size_t)r * row_stride + c2) : "memory");
         }
     }
 #pragma unroll
     for (int i = 0; i < PER_THREAD; ++i) {
         const int e = threadIdx.x + i * P_THREADS, r = e / PAIRS, c2 = (e - r * PAIRS) * 2;
-        *reinterpret_cast<float2*>(&dst[r * dst_ld + c2]) = v[i];
+        *reinterpret_cast<float2*>(&dst[r * dst_ld + c2]) = make_float2(__uint_as_float(x0[i]), __uint_as_float(x1[i]));
     }
 }
 
@@ -367,9 +362,11 @@ train_persist_kernel(PersistArgs a) {
     const int B = a.B;
     const float invB = 1.0f / (float)B;
     const float scale = a.train ? 1.25f : 1.0f;
-    unsigned long long bar_target = 0, ready_base = 0;     // used by BAR_TID / thread 0 only
-    if (tid == BAR_TID) bar_target = (ld_acquire64(&a.bar[0]) / gridDim.x) * gridDim.x;
-    if (tid == BAR_TID) ready_base = ld_acquire64(&a.bar[1]);   // nobody bumps it before the first barrier pair completes
+    unsigned long long* const ready = a.ctl + CTRL_READY64;
+    if (tid == 0) {
+        s.epoch0 = ld_acquire64(a.ctl + CTRL_EPOCH64);      // steps this workspace has seen: the base of the step tags
+        s.ready_base = ld_acquire64(ready);                 // nobody bumps it before every row CTA has produced step 0's rows
+    }
     unsigned long long ready_seen = 0;
     s.lut[tid] = decode_px(tid);
 
@@ -377,6 +374,9 @@ train_persist_kernel(PersistArgs a) {
     const int mt = cta / N_NT, nt = cta - mt * N_NT;
     const int nchunks = (B + CR - 1) / CR;
     const bool single = nchunks == 1;                 // batch <= 64: the pixel tile is prefetched a step ahead
+    // home rank of this thread's gradient values in the two-stage exchange (slices of every tile, see ll_allreduce)
+    const int home_w1 = DDP ? (tid * a.world) / W1_ACTIVE : 0;
+    const int home_sm = DDP ? (tid * a.world) >> 8 : 0;
     PixelRegs px;
     if (own_w1) {
         for (int t = tid; t < MT * (NT / 4); t += P_THREADS) {
@@ -389,16 +389,22 @@ train_persist_kernel(PersistArgs a) {
             tile_load<FEED>(px, a, a.idx, 0, nt);
         }
     }
-    __syncthreads();                                   // lut ready
+    __syncthreads();                                   // lut, epoch0 ready
+    const unsigned long long epoch0 = s.epoch0;
     if (own_w1 && single) tile_store(px, s, s.xs[0]);
     __syncthreads();
 
 // clock stamp that cannot be taken before a preceding bar.sync has actually released (BAR is
 // deferred-blocking: a bare clock read right after it reports the issue time): read a shared word first
+#ifdef DDPM_DBG_GLOBALTIMER      /* nanoseconds on one clock for the whole GPU: lines CTAs up against each other */
+#define DBG_CLOCK_ASM(t, dep) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep) : "memory")
+#else
+#define DBG_CLOCK_ASM(t, dep) asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) : "r"(dep) : "memory")
+#endif
 #define DBG_STAMP(slot) do { if (a.dbg && tid == 0 && step < 8) { \
         unsigned v__; long long t__; \
         asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v__) : "r"((unsigned)__cvta_generic_to_shared(&s.zs[0])) : "memory"); \
-        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t__) : "r"(v__) : "memory"); \
+        DBG_CLOCK_ASM(t__, v__); \
         a.dbg[((size_t)cta * 8 + step) * 16 + (slot)] = t__; } } while (0)
     for (int step = 0; step < a.nsteps; ++step) {
         DBG_STAMP(0);
@@ -407,17 +413,45 @@ train_persist_kernel(PersistArgs a) {
         float* xs_cur = s.xs[step & 1];
         const bool prefetch = own_w1 && single && (step + 1 < a.nsteps);
         constexpr bool ddp = DDP;
-        const bool actx = ddp && a.act_exchange && single;           // W1 through the dz1 exchange
-        const bool actx_all = actx && a.act_exchange == 2;           // ... and W2 / W3 / biases through dz2, h1d, h2, dz3
-        const unsigned long long T = a.comm_step + step + 1;            // global step number of this communicator
+        const bool actx = ddp && a.act_exchange && single;           // W1's gradient through the dz1 exchange
+        const unsigned long long T = a.comm_step + step + 1;         // step number of this communicator (cross-GPU tags)
+        const unsigned long long TL = epoch0 + step + 1;             // step number of this workspace (in-GPU tags)
+        const unsigned tl = (unsigned)TL;
+        const size_t parl = (size_t)(TL & 1);
+        unsigned long long* const my_part = a.llpart + parl * N_NT * B * HID;
+        unsigned long long* const my_act = a.llact + parl * B * LL_ACT_WORDS;
+        unsigned long long* const my_loss = a.llloss + parl * B;
         float host_loss = 0.f;
         unsigned long long feed_probe = 0;
+        // Row CTAs fetch this step's W2 (into registers: thread (jb, kb) keeps the 8x8 block W2[jb*8.., kb*8..], used by
+        // both the forward product, reduced over kb, and the backward product, reduced over jb) and W3 / b2 (into smem).
+        // They may do so once the 'ready' counter shows that the 36 owner CTAs finished last step's updates, which is
+        // about 1,000-1,700 cycles into this step.  EVERY thread samples the counter itself at the top of the step and
+        // looks at its sample at two points inside phase A: no broadcast, no barrier, and the 64 KB arrive while phase A
+        // computes (issued after phase A, they held the partial-sum polls up for ~3,000 cycles: 64 SMs pull the same
+        // lines).  (No fence: the owners released their updates before bumping the counter; the loads below are
+        // L2-coherent .cg / cp.async loads issued after the sample showed the count.)
+        float blk[8][8];
+        bool params_loaded = false;
+        const unsigned long long ready_need = s.ready_base + (unsigned long long)N_READY * step;
+        if (cta < B && step > 0) ready_seen = ld_relaxed64(ready);
+#define PARAM_LOADS() do { \
+            load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15); \
+            for (int t__ = tid; t__ < NC * HID / 4; t__ += P_THREADS) \
+                __pipeline_memcpy_async(&s.w3[t__ * 4], a.params + DDPM_OFF_W3 + t__ * 4, 16); \
+            if (tid < HID / 4) __pipeline_memcpy_async(&s.b2[tid * 4], a.params + DDPM_OFF_B2 + tid * 4, 16); \
+            else if (tid < HID / 2 && step == 0) __pipeline_memcpy_async(&s.b1[(tid - HID / 4) * 4], a.params + DDPM_OFF_B1 + (tid - HID / 4) * 4, 16); \
+            __pipeline_commit(); params_loaded = true; DBG_STAMP(13); } while (0)
+#define PARAM_LOADS_TRY() do { if (cta < B && !params_loaded) { \
+            if (step == 0 || ready_seen >= ready_need) PARAM_LOADS(); \
+            else ready_seen = ld_relaxed64(ready); } } while (0)
 
         // ================================ phase A ================================
         if (own_w1) {
             const int m = tid & 15, rg = tid >> 4;            // 16 row groups x 4 rows
+            // (tried: 4 rows x 4 units per thread over four K slices combined through smem - half the LDS per FMA, but
+            //  bank conflicts between row groups and the extra pass made phase A 13 % slower; not kept)
             if (prefetch) tile_load_idx(px, a, idx + B, 0);   // next step's sample indices: in flight during phase A
-            if (tid == BAR_TID && step > 0 && cta < B) ready_seen = ld_relaxed64(&a.bar[1]);
             // early probe of the next step's sequence word by every thread: the load is in flight during phase A and
             // is looked at only before the pixel loads (a probe through shared memory would put an L2 round trip in
             // front of the bar.sync below: + 0.7 us per step, measured)
@@ -434,6 +468,10 @@ train_persist_kernel(PersistArgs a) {
                 float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int n4 = 0; n4 < NT / 4; ++n4) {
+                    // looks at the counter: six, ~200 ns apart, on one GPU (the count is there within the first two); with
+                    // a cross-GPU exchange in front of it the count comes late and every look would wait for the previous
+                    // sample's round trip (+2,000 cycles of phase A, measured): two looks then
+                    if (single && (DDP ? (n4 == 5 || n4 == 11) : ((n4 & 1) && n4 < 13))) PARAM_LOADS_TRY();
                     const float4 w = *reinterpret_cast<const float4*>(&s.w1t[w1_idx(m, n4 * 4)]);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
@@ -445,85 +483,74 @@ train_persist_kernel(PersistArgs a) {
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
                     const int row = c * CR + rg * 4 + r;
-                    if (row < B) a.part[((size_t)nt * B + row) * HID + mt * MT + m] = acc[r];
+                    if (row < B) ll_store1(my_part + ((size_t)nt * B + row) * HID + mt * MT + m, tl, acc[r]);
                 }
             }
             // next step's pixels do not depend on the weights: start fetching them now, decode
-            // them after phase B; the two round trips hide behind the barrier waits
-            if (prefetch && tid != BAR_TID) {
-                if (FEED && feed_probe != a.feed_g0 + (unsigned long long)step + 2) feed_wait(a, step + 1);
-                tile_load_px<FEED>(px, a, nt);
-            }
-        }
-        DBG_STAMP(1);
-        grid_arrive(a.bar, bar_target);
-        // While the barrier completes: fetch this step's W2 into REGISTERS — thread (jb, kb) keeps the
-        // 8x8 block W2[jb*8.., kb*8..], used by both the forward product (reduced over kb) and the
-        // backward product (reduced over jb) — and W3 / b1 / b2 into smem.  Their 36 owner CTAs bumped
-        // the 'ready' counter after last step's updates, long before this point.
-        float blk[8][8];
-        int yv_first = 0;
-        if (cta < B) {
-            if (step > 0) {
-                // normally satisfied by the sample taken at the start of phase A (the 36 owners finish early)
-                // (no fence: the owners released their updates before bumping the counter, and W2/W3/b are
-                //  read below with L2-coherent .cg loads that are issued only after this check succeeded)
-                if (tid == BAR_TID) {
-                    const unsigned long long need = ready_base + (unsigned long long)N_READY * step;
-                    while (ready_seen < need) ready_seen = ld_relaxed64(&a.bar[1]);
-                }
-                __syncthreads();
-            }
-            if (tid != BAR_TID) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
-            for (int t = tid; t < NC * HID / 4; t += P_THREADS)
-                __pipeline_memcpy_async(&s.w3[t * 4], a.params + DDPM_OFF_W3 + t * 4, 16);
-            if (tid < HID / 4) __pipeline_memcpy_async(&s.b1[tid * 4], a.params + DDPM_OFF_B1 + tid * 4, 16);
-            else if (tid < HID / 2) __pipeline_memcpy_async(&s.b2[(tid - HID / 4) * 4], a.params + DDPM_OFF_B2 + (tid - HID / 4) * 4, 16);
-            __pipeline_commit();
-            if (tid == 32) {                                  // label of this CTA's first row: two dependent loads,
-                const int64_t sidx = __ldg(idx + cta);        // kept off the barrier thread and off warp 0
-                if (FEED) feed_wait(a, step);
-                const bool ok = sidx >= 0 && sidx < a.n_samples;
-                yv_first = !ok ? 0 : (FEED ? __ldcg(a.labels + sidx) : __ldg(a.labels + sidx));
-            }
-        }
-        grid_wait(a.bar, bar_target);
-        // the barrier thread kept its own memory pipeline empty while it was fencing; it catches up now
-        if (tid == BAR_TID) {
-            if (cta < B) load_w2_block(blk, a.params + DDPM_OFF_W2, tid >> 4, tid & 15);
+            // them after phase B; the two round trips hide behind the waits for the rows
             if (prefetch) {
                 if (FEED && feed_probe != a.feed_g0 + (unsigned long long)step + 2) feed_wait(a, step + 1);
                 tile_load_px<FEED>(px, a, nt);
             }
         }
-        DBG_STAMP(2);
+        DBG_STAMP(1);
 
         // ================================ phase B ================================
         if (cta < B) {
             const int j = tid & 127, h = tid >> 7;
             const int jb = tid >> 4, kb = tid & 15;
+            if (!params_loaded) {                             // not seen during phase A (or no phase A in this CTA): wait
+                const long long t0 = clock64();
+                unsigned spins = 0;
+                while (step > 0 && ready_seen < ready_need) {
+                    if (poll_miss(a.lerr, t0, spins)) break;
+                    ready_seen = ld_relaxed64(ready);
+                }
+                PARAM_LOADS();
+            }
+            DBG_STAMP(14);
             float* red2 = s.w2;                               // [16][RLD] partial products (padded: conflict-free float4 stores)
             constexpr int RLD = HID + 4;
             bool staged = false;
             for (int row = cta; row < B; row += gridDim.x) {
-                if (tid == 32) {
-                    int yv = yv_first;
-                    if (row != cta) {
-                        const int64_t sidx = __ldg(idx + row);
-                        const bool ok = sidx >= 0 && sidx < a.n_samples;
-                        yv = !ok ? 0 : (FEED ? __ldcg(a.labels + sidx) : __ldg(a.labels + sidx));
-                    }
-                    s.ylab = yv;                              // read by warp 0 after three more barriers
+                if (tid == 32) {                              // label of this row: two dependent loads, off warp 0
+                    const int64_t sidx = __ldg(idx + row);
+                    if (FEED) feed_wait(a, step);
+                    const bool ok = sidx >= 0 && sidx < a.n_samples;
+                    s.ylab = !ok ? 0 : (FEED ? __ldcg(a.labels + sidx) : __ldg(a.labels + sidx));   // read after three more barriers
                 }
                 // ---- 1. z1 = sum of the 14 tile partials (two fixed halves) + b1 ; ReLU ; dropout
-                float zp = 0.f;
+                float zp = 0.f, b1v = 0.f;
                 {
-                    const float* p = a.part + ((size_t)(h * 7) * B + row) * HID + j;
-                    float v[7];
+                    const unsigned long long* p = my_part + ((size_t)(h * 7) * B + row) * HID + j;
+                    unsigned vx[7], vf[7];
 #pragma unroll
-                    for (int i = 0; i < 7; ++i) v[i] = __ldcg(p + (size_t)i * B * HID);
+                    for (int i = 0; i < 7; ++i)
+                        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx[i]), "=r"(vf[i])
+                                     : "l"(p + (size_t)i * B * HID) : "memory");
+                    // b1 as updated in the last step (its tagged word): in flight together with the partial sums
+                    const bool poll_b1 = step > 0 && h == 0;
+                    const unsigned long long* pb = a.llb1 + parl * HID + j;
+                    unsigned bx = 0, bf = tl;
+                    if (poll_b1) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(bx), "=r"(bf) : "l"(pb) : "memory");
+                    const long long t0 = clock64();
+                    unsigned spins = 0;
+                    for (;;) {                                // re-issue everything still missing, together
+                        bool missing = bf != tl;
 #pragma unroll
-                    for (int i = 0; i < 7; ++i) zp += v[i];
+                        for (int i = 0; i < 7; ++i) missing |= vf[i] != tl;
+                        if (!missing || poll_miss(a.lerr, t0, spins)) break;
+                        if (bf != tl) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(bx), "=r"(bf) : "l"(pb) : "memory");
+#pragma unroll
+                        for (int i = 0; i < 7; ++i)
+                            if (vf[i] != tl)
+                                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx[i]), "=r"(vf[i])
+                                             : "l"(p + (size_t)i * B * HID) : "memory");
+                    }
+                    b1v = __uint_as_float(bx);
+                    if (row == cta) DBG_STAMP(15);
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) zp += __uint_as_float(vx[i]);
                 }
                 bool keep = true;
                 if (a.train && h == 0) {
@@ -531,15 +558,17 @@ train_persist_kernel(PersistArgs a) {
                     else keep = philox_keep(a.seed, a.step0 + step, (uint32_t)(row * HID + j));
                 }
                 s.red[h * HID + j] = zp;
-                if (!staged) { __pipeline_wait_prior(0); staged = true; }
+                if (row == cta) DBG_STAMP(12);
+                if (!staged) { __pipeline_wait_prior(0); staged = true; }    // W3 / b2 (/ b1 at step 0) are in smem
                 __syncthreads();
+                if (row == cta) DBG_STAMP(2);
                 DBG_STAMP(6);
+                unsigned long long* const arow = my_act + (size_t)row * LL_ACT_WORDS;
                 float h1 = 0.f;
                 if (h == 0) {
-                    const float z = (s.red[j] + s.red[HID + j]) + s.b1[j];
+                    const float z = (s.red[j] + s.red[HID + j]) + (step > 0 ? b1v : s.b1[j]);
                     h1 = (z > 0.f && keep) ? z * scale : 0.f;
-                    a.h1d[(size_t)row * HID + j] = h1;
-                    if (actx_all) act_push(a, T, row, ACT_H1D + j, h1);
+                    ll_store1(arow + ACT_H1D + j, tl, h1);
                     s.hs[j] = h1;
                 }
                 __syncthreads();
@@ -568,8 +597,7 @@ train_persist_kernel(PersistArgs a) {
                     z2 += s.b2[j];
                     gate2 = z2 > 0.f;
                     const float hv = gate2 ? z2 : 0.f;
-                    a.h2[(size_t)row * HID + j] = hv;
-                    if (actx_all) act_push(a, T, row, ACT_H2 + j, hv);
+                    ll_store1(arow + ACT_H2 + j, tl, hv);
                     s.h2s[j] = hv;
                 }
                 __syncthreads();
@@ -591,41 +619,40 @@ train_persist_kernel(PersistArgs a) {
                     if (lane == 0) { s.zs[2 * warp] = v0; s.zs[2 * warp + 1] = v1; }
                 }
                 __syncthreads();
-                // ---- 4. log-softmax / NLL / dlogits by warp 0 (lane c < 10 holds class c)
-                if (warp == 0) {
-                    const float z = lane < NC ? s.zs[lane] : -INFINITY;
-                    float m = z;
-#pragma unroll
-                    for (int o = 8; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));   // classes live in lanes 0..9
-                    const float e = lane < NC ? expf(z - m) : 0.f;
-                    float sum = e;
-#pragma unroll
-                    for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                    m = __shfl_sync(0xffffffffu, m, 0);
-                    sum = __shfl_sync(0xffffffffu, sum, 0);
-                    const int yv = s.ylab;
-                    const float zy = __shfl_sync(0xffffffffu, z, yv);
-                    if (lane == 0) a.rowloss[row] = -((zy - m) - logf(sum));
-                    if (lane < NCP) {
-                        const float d = lane < NC ? (e / sum - (lane == yv ? 1.f : 0.f)) * invB : 0.f;
-                        s.dzs[lane] = d;
-                        a.dz3[(size_t)row * NCP + lane] = d;
-                        if (actx_all) act_push(a, T, row, ACT_DZ3 + lane, d);
-                    }
-                }
-                __syncthreads();
-                DBG_STAMP(8);
-                // ---- 5. dz2 = (dz3 . W3) * (z2 > 0)
+                // ---- 4+5. log-softmax / NLL / dlogits, evaluated by every thread of the first half from the ten logits
+                //      in smem (no warp-0 section, no extra barrier), then dz2 = (dz3 . W3) * (z2 > 0)
                 if (h == 0) {
-                    float d = 0.f;
+                    float z[NC], e[NC];
+                    {
+                        const float4 z0 = *reinterpret_cast<const float4*>(&s.zs[0]);
+                        const float4 z1 = *reinterpret_cast<const float4*>(&s.zs[4]);
+                        const float2 z2v = *reinterpret_cast<const float2*>(&s.zs[8]);
+                        z[0] = z0.x; z[1] = z0.y; z[2] = z0.z; z[3] = z0.w; z[4] = z1.x; z[5] = z1.y; z[6] = z1.z; z[7] = z1.w;
+                        z[8] = z2v.x; z[9] = z2v.y;
+                    }
+                    float mx = z[0];
 #pragma unroll
-                    for (int c = 0; c < NC; ++c) d = fmaf(s.dzs[c], s.w3[c * HID + j], d);
+                    for (int c = 1; c < NC; ++c) mx = fmaxf(mx, z[c]);
+                    float sum = 0.f;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) { e[c] = expf(z[c] - mx); sum += e[c]; }
+                    const int yv = s.ylab;
+                    float d = 0.f, dmine = 0.f, zy = 0.f;
+#pragma unroll
+                    for (int c = 0; c < NC; ++c) {
+                        const float dc = (e[c] / sum - (c == yv ? 1.f : 0.f)) * invB;
+                        d = fmaf(dc, s.w3[c * HID + j], d);
+                        if (c == j) dmine = dc;
+                        if (c == yv) zy = z[c];
+                    }
+                    if (j < NCP) ll_store1(arow + ACT_DZ3 + j, tl, dmine);          // classes 10..15: zero padding
+                    if (j == 0) ll_store1(my_loss + row, tl, -((zy - mx) - logf(sum)));
                     d = gate2 ? d : 0.f;
-                    a.dz2[(size_t)row * HID + j] = d;
-                    if (actx_all) act_push(a, T, row, ACT_DZ2 + j, d);
+                    ll_store1(arow + ACT_DZ2 + j, tl, d);
                     s.ds[j] = d;
                 }
                 __syncthreads();
+                DBG_STAMP(8);
                 // ---- 6. dz1 = (dz2 . W2) * scale * (kept && z1 > 0): same blocks, reduced over the 16 row blocks
                 {
                     const float4 d0 = *reinterpret_cast<const float4*>(&s.ds[jb * 8]);
@@ -648,30 +675,37 @@ train_persist_kernel(PersistArgs a) {
 #pragma unroll
                     for (int q = 0; q < 16; ++q) v += red2[q * RLD + j];
                     const float dzv = (h1 > 0.f) ? v * scale : 0.f;
-                    a.dz1[(size_t)row * HID + j] = dzv;
-                    if (actx) act_push(a, T, row, ACT_DZ1 + j, dzv);
+                    ll_store1(arow + ACT_DZ1 + j, tl, dzv);
+                    if (actx) {                               // the same word to every peer (dz1 exchange)
+                        const size_t slot = (((size_t)(T & 1) * a.world + a.rank) * CR + row) * XACT_ROW_WORDS + j;
+                        for (int r = 0; r < a.world; ++r)
+                            if (r != a.rank) ll_store1(a.xrecv_dz[r] + slot, (unsigned)T, dzv);
+                    }
                 }
                 __syncthreads();
             }
-            if (!staged) __pipeline_wait_prior(0);
         }
         if (prefetch) tile_store(px, s, s.xs[(step + 1) & 1]);    // the other buffer: phase C below still reads xs_cur
         DBG_STAMP(3);
-        grid_barrier(a.bar, bar_target);
-        DBG_STAMP(4);
 
         // ================================ phase C ================================
         if (own_w1) {
             // thread -> (batch quarter qd, 4 units mq*4.., 4 pixels n4*4..): 16 FMAs per two LDS.128
-            const bool act = tid < 4 * 4 * (NT / 4);            // 224 threads
+            const bool act = tid < W1_ACTIVE;                   // 224 threads
             const int qd = tid / 56, u = tid - qd * 56, mq = u / (NT / 4), n4 = u - mq * (NT / 4);
-            float acc[4][4];
+            // db1 of this tile's 16 units: by 16 threads of the otherwise idle warp 7 of the pixel-tile-0 CTAs, from the
+            // dz1 tile every W1 CTA stages anyway.  The updated bias goes to the next step's rows as tagged words (no
+            // release fence in this CTA: its next phase A is on everybody's critical path).
+            const bool b1_thread = nt == 0 && tid >= W1_ACTIVE && tid < W1_ACTIVE + MT;
+            const int offb1 = DDPM_OFF_B1 + mt * MT + (tid - W1_ACTIVE);
+            const float pold_b1 = b1_thread ? __ldcg(a.params + offb1) : 0.f;
             float db_acc = 0.f;
+            float acc[4][4];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int jx = 0; jx < 4; ++jx) acc[i][jx] = 0.f;
-            // activation-exchange mode: one pass per SOURCE RANK, in rank order on every rank (identical sums);
+            // dz1-exchange mode: one pass per SOURCE RANK, in rank order on every rank (identical sums);
             // the next remote source's pixel tile is fetched while the current one is being multiplied
             const int npass = actx ? a.world : nchunks;
             int nxt = -1;
@@ -684,24 +718,25 @@ train_persist_kernel(PersistArgs a) {
                 const float* xs_src = xs_cur;
                 if (!actx) {
                     if (!single) { tile_load<FEED>(px, a, idx, c * CR, nt); tile_store(px, s, xs_cur); }
-                } else if (c != a.rank) {
+                    const int nrows = B - c * CR < CR ? B - c * CR : CR;
+                    ll_stage<MT>(my_act + (size_t)(c * CR) * LL_ACT_WORDS + ACT_DZ1 + mt * MT, LL_ACT_WORDS, nrows, tl,
+                                 s.dzt, MT, a.lerr);
+                } else if (c == a.rank) {
+                    ll_stage<MT>(my_act + ACT_DZ1 + mt * MT, LL_ACT_WORDS, B, tl, s.dzt, MT, a.lerr);
+                } else {
                     tile_store(px, s, s.xsx);
                     xs_src = s.xsx;
                     nxt = c + 1 + ((c + 1 == a.rank) ? 1 : 0);
                     if (nxt < a.world) tile_load<FEED>(px, a, a.idx_all + (size_t)nxt * a.idx_stride + (size_t)step * B, 0, nt);
-                }
-                if (!actx) {
-                    const int r = tid >> 2, q = tid & 3, row = c * CR + r;      // 64 rows x 4 float4
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (row < B) v = __ldcg(reinterpret_cast<const float4*>(a.dz1 + (size_t)row * HID + mt * MT) + q);
-                    *reinterpret_cast<float4*>(&s.dzt[r * MT + q * 4]) = v;
-                } else {
-                    act_stage<MT>(a, T, c, s.dzt, MT, a.dz1, HID, mt * MT, ACT_DZ1);   // rank c's dz1 rows, this tile's columns
+                    // rank c's dz1 rows, this tile's columns, from the words it pushed into this rank's buffer
+                    ll_stage<MT>(a.xrecv_dz[a.rank] + (((size_t)(T & 1) * a.world + c) * CR) * XACT_ROW_WORDS + mt * MT,
+                                 XACT_ROW_WORDS, B, (unsigned)T, s.dzt, MT, a.xerr);
                 }
                 __syncthreads();
+                if (c == 0) DBG_STAMP(4);
                 DBG_STAMP(9);
-                if (nt == 0 && tid >= 224 && tid < 224 + MT) {        // db1 for this tile's 16 units (idle warp)
-                    const int m = tid - 224;
+                if (b1_thread) {
+                    const int m = tid - W1_ACTIVE;
                     float p[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                     for (int r = 0; r < CR; r += 4) {
@@ -724,17 +759,6 @@ train_persist_kernel(PersistArgs a) {
                     }
                 }
             }
-            if (nt == 0 && tid >= 224 && tid < 224 + MT) {
-                const int offb = DDPM_OFF_B1 + mt * MT + (tid - 224);
-                float gb[1] = {db_acc * a.gscale};
-                const float pold = __ldcg(a.params + offb);
-                if (ddp && !actx) ll_allreduce<1>(a, T, cta, offb, gb);
-                grad_out(a.grads, a.lr, a.params, offb, gb[0], pold);
-                // b1 is read by every row CTA at the start of the next step: its 8 writers count towards 'ready' too
-                // (row CTAs that own no W1 tile - batch > 112 - get there long before this CTA leaves phase C)
-                __syncwarp(0x0000ffffu);
-                if (tid == 224 && a.lr != 0.f) red_release64(&a.bar[1]);
-            }
             float* pbuf = s.w2;                                  // [4 quarters][16 units][56 px] partial gradients
             if (act) {
 #pragma unroll
@@ -755,9 +779,9 @@ train_persist_kernel(PersistArgs a) {
                 g[2] = ((p[0].z + p[1].z) + (p[2].z + p[3].z)) * a.gscale;
                 g[3] = ((p[0].w + p[1].w) + (p[2].w + p[3].w)) * a.gscale;
                 const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
-                if (ddp && !actx) {                             // push to every peer, then sum everyone's tile
+                if (ddp && !actx) {                             // exchange with every peer, then everyone holds the sum
                     DBG_STAMP(11);
-                    ll_allreduce<4>(a, T, cta, off, g);
+                    ll_allreduce<4>(a, T, home_w1, off, g);
                     DBG_STAMP(12);
                 }
                 if (a.grads) *reinterpret_cast<float4*>(a.grads + off) = make_float4(g[0], g[1], g[2], g[3]);
@@ -767,6 +791,13 @@ train_persist_kernel(PersistArgs a) {
                     w.z = fmaf(-a.lr, g[2], w.z); w.w = fmaf(-a.lr, g[3], w.w);
                     *reinterpret_cast<float4*>(&s.w1t[w1_idx(m, n4b * 4)]) = w;
                 }
+            } else if (b1_thread) {                              // alongside the tile update above
+                float gb[1] = {db_acc * a.gscale};
+                if (ddp && !actx) ll_allreduce<1>(a, T, (tid - W1_ACTIVE) % a.world, offb1, gb);
+                grad_out(a.grads, a.lr, a.params, offb1, gb[0], pold_b1);
+                if (a.lr != 0.f)
+                    ll_store1(a.llb1 + (size_t)((TL + 1) & 1) * HID + mt * MT + (tid - W1_ACTIVE), (unsigned)(TL + 1),
+                              fmaf(-a.lr, gb[0], pold_b1));
             }
         } else if (cta < CTA_W3) {
             // ---- dW2 tile [16 rows jt][32 cols kt].  thread -> (batch quarter bq, 4 rows jq*4.., 2 cols k2*2..):
@@ -782,24 +813,14 @@ train_persist_kernel(PersistArgs a) {
             const float pbias = do_db ? __ldcg(a.params + DDPM_OFF_B2 + jt * 16 + tid) : 0.f;
             float acc[4][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
             float db_acc = 0.f;
-            for (int c = 0; c < (actx_all ? a.world : nchunks); ++c) {   // actx_all: one pass per source rank, in rank order
+            for (int c = 0; c < nchunks; ++c) {
                 __syncthreads();
-                if (actx_all) {
-                    act_stage<MT>(a, T, c, s.dzt, MT, a.dz2, HID, jt * 16, ACT_DZ2);
-                    act_stage<32>(a, T, c, hst, 32, a.h1d, HID, kt * 32, ACT_H1D);
-                } else {
-                    const int r = tid >> 2, q = tid & 3, row = c * CR + r;
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f), u0 = v, u1 = v;
-                    if (row < B) {
-                        v = __ldcg(reinterpret_cast<const float4*>(a.dz2 + (size_t)row * HID + jt * 16) + q);
-                        u0 = __ldcg(reinterpret_cast<const float4*>(a.h1d + (size_t)row * HID + kt * 32) + q);
-                        u1 = __ldcg(reinterpret_cast<const float4*>(a.h1d + (size_t)row * HID + kt * 32) + q + 4);
-                    }
-                    *reinterpret_cast<float4*>(&s.dzt[r * MT + q * 4]) = v;
-                    *reinterpret_cast<float4*>(&hst[r * 32 + q * 4]) = u0;
-                    *reinterpret_cast<float4*>(&hst[r * 32 + q * 4 + 16]) = u1;
-                }
+                const int nrows = B - c * CR < CR ? B - c * CR : CR;
+                const unsigned long long* rows0 = my_act + (size_t)(c * CR) * LL_ACT_WORDS;
+                ll_stage<32>(rows0 + ACT_H1D + kt * 32, LL_ACT_WORDS, nrows, tl, hst, 32, a.lerr);     // produced first
+                ll_stage<MT>(rows0 + ACT_DZ2 + jt * 16, LL_ACT_WORDS, nrows, tl, s.dzt, MT, a.lerr);
                 __syncthreads();
+                if (c == 0) DBG_STAMP(4);
 #pragma unroll
                 for (int rr = 0; rr < CR / 4; ++rr) {
                     const int r = bq * (CR / 4) + rr;
@@ -830,14 +851,14 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
                 float g[2] = {((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale,
                               ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale};
-                if (ddp && !actx_all) ll_allreduce<2>(a, T, cta, off, g);
+                if (ddp) ll_allreduce<2>(a, T, home_sm, off, g);
                 grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
                 grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
             }
             if (do_db) {
                 const int offb = DDPM_OFF_B2 + jt * 16 + tid;
                 float gb[1] = {db_acc * a.gscale};
-                if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, offb, gb);
+                if (ddp) ll_allreduce<1>(a, T, tid % a.world, offb, gb);
                 grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
             }
         } else {
@@ -850,31 +871,17 @@ train_persist_kernel(PersistArgs a) {
             const int c0 = tid >> 5, c1 = c0 + 8;                // final pass: classes c0 and (threads < 64) c1
             const float p0 = __ldcg(a.params + DDPM_OFF_W3 + c0 * HID + kt * 32 + k);
             const float p1 = c1 < NC ? __ldcg(a.params + DDPM_OFF_W3 + c1 * HID + kt * 32 + k) : 0.f;
-            float lsum = 0.f;
-            if (kt == 2) {                                       // per-row losses: loaded now, reduced at the end
-                for (int row = tid; row < B; row += P_THREADS) lsum += __ldcg(a.rowloss + row);
-            }
             float acc[NC];
 #pragma unroll
             for (int i = 0; i < NC; ++i) acc[i] = 0.f;
-            for (int c = 0; c < (actx_all ? a.world : nchunks); ++c) {
+            for (int c = 0; c < nchunks; ++c) {
                 __syncthreads();
-                if (actx_all) {
-                    act_stage<NCP>(a, T, c, s.dzt, MT, a.dz3, NCP, 0, ACT_DZ3);
-                    act_stage<32>(a, T, c, hst, 32, a.h2, HID, kt * 32, ACT_H2);
-                } else {
-                    const int r = tid >> 2, q = tid & 3, row = c * CR + r;
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f), u0 = v, u1 = v;
-                    if (row < B) {
-                        v = __ldcg(reinterpret_cast<const float4*>(a.dz3 + (size_t)row * NCP) + q);
-                        u0 = __ldcg(reinterpret_cast<const float4*>(a.h2 + (size_t)row * HID + kt * 32) + q);
-                        u1 = __ldcg(reinterpret_cast<const float4*>(a.h2 + (size_t)row * HID + kt * 32) + q + 4);
-                    }
-                    *reinterpret_cast<float4*>(&s.dzt[r * MT + q * 4]) = v;
-                    *reinterpret_cast<float4*>(&hst[r * 32 + q * 4]) = u0;
-                    *reinterpret_cast<float4*>(&hst[r * 32 + q * 4 + 16]) = u1;
-                }
+                const int nrows = B - c * CR < CR ? B - c * CR : CR;
+                const unsigned long long* rows0 = my_act + (size_t)(c * CR) * LL_ACT_WORDS;
+                ll_stage<32>(rows0 + ACT_H2 + kt * 32, LL_ACT_WORDS, nrows, tl, hst, 32, a.lerr);
+                ll_stage<NCP>(rows0 + ACT_DZ3, LL_ACT_WORDS, nrows, tl, s.dzt, MT, a.lerr);
                 __syncthreads();
+                if (c == 0) DBG_STAMP(4);
 #pragma unroll
                 for (int rr = 0; rr < CR / 8; ++rr) {
                     const int r = bq * (CR / 8) + rr;
@@ -888,6 +895,15 @@ train_persist_kernel(PersistArgs a) {
                     acc[9] = fmaf(d2.y, hv, acc[9]);
                 }
             }
+            float lsum = 0.f;
+            if (kt == 2) {                                       // per-row losses (stored before that row's dz3)
+                const long long t0 = clock64();
+                for (int row = tid; row < B; row += P_THREADS) {
+                    float lv[1];
+                    ll_poll<1>(a.lerr, my_loss + row, tl, t0, lv);
+                    lsum += lv[0];
+                }
+            }
 #pragma unroll
             for (int i = 0; i < NC; ++i) pb[(bq * NC + i) * 32 + k] = acc[i];
             if (kt == 2) s.red[tid] = lsum;
@@ -898,13 +914,13 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
                 const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
                 float ga[1] = {g0 * a.gscale};
-                if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, o0, ga);
+                if (ddp) ll_allreduce<1>(a, T, home_sm, o0, ga);
                 grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) {
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
                     float gc[1] = {g1 * a.gscale};
-                    if (ddp && !actx_all) ll_allreduce<1>(a, T, cta, o1, gc);
+                    if (ddp) ll_allreduce<1>(a, T, home_sm, o1, gc);
                     grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
                 }
             }
@@ -925,14 +941,13 @@ train_persist_kernel(PersistArgs a) {
                 }
             }
         }
-        if (!own_w1 && a.lr != 0.f) {                         // W2 / W3 / b1 / b2 of the next step are in place
+        if (!own_w1 && a.lr != 0.f) {                         // W2 / W3 / b2 of the next step are in place
             __syncthreads();
-            if (tid == 0) red_release64(&a.bar[1]);
+            if (tid == 0) red_release64(ready);
         }
         if (FEED && a.loss_steps && tid == 0 && cta == CTA_W3 + 2) a.loss_steps[step] = host_loss;
         DBG_STAMP(5);
-        // no barrier here: W1 tiles are private; everything else is ordered by the next step's
-        // first barrier (phase B of step t+1 starts only after every CTA finished phase C of t)
+        // nothing else orders step t+1 after step t: W1 tiles are private, everything else is gated by tags / 'ready'
     }
 
     // write the owned W1 tile back
@@ -942,6 +957,65 @@ train_persist_kernel(PersistArgs a) {
             const int m = t / (NT / 4), q = t - m * (NT / 4);
             const float4 v = *reinterpret_cast<const float4*>(&s.w1t[w1_idx(m, q * 4)]);
             *reinterpret_cast<float4*>(a.params + DDPM_OFF_W1 + (size_t)(mt * MT + m) * IN + nt * NT + q * 4) = v;
+        }
+    }
+    // the last CTA to leave advances the workspace's step count (the tag base of the next launch).  Every CTA read it at
+    // the top of the kernel, and a CTA can only finish after all CTAs took part in the last step.
+    if (tid == 0) {
+        const unsigned long long old = atomicAdd(a.ctl + CTRL_FIN64, 1ULL);
+        if (old % gridDim.x == gridDim.x - 1) a.ctl[CTRL_EPOCH64] = epoch0 + (unsigned long long)a.nsteps;
+    }
+}
+
+// The gradient exchange alone (measurement aid + test of the exchange): the same threads exchange the same elements
+// of the 473,088-byte bucket as in train_persist_kernel<*, true>, `nsteps` times, with no forward/backward work.
+// Contribution of rank r to element e at step t: (r + 1) * (1 + (e & 1023)) / 1024 + t (exactly representable sums).
+__global__ void __launch_bounds__(P_THREADS, 1)
+exchange_only_kernel(PersistArgs a) {
+    const int tid = threadIdx.x, cta = blockIdx.x;
+    const int home_w1 = (tid * a.world) / W1_ACTIVE, home_sm = (tid * a.world) >> 8;
+    const float rk = (float)(a.rank + 1);
+    auto contrib = [&](int e, int step) { return rk * (float)(1 + (e & 1023)) * (1.0f / 1024.0f) + (float)(step & 255); };
+    for (int step = 0; step < a.nsteps; ++step) {
+        const unsigned long long T = a.comm_step + step + 1;
+        const bool last = a.xout != nullptr && step == a.nsteps - 1;
+        if (cta < N_W1) {
+            const int mt = cta / N_NT, nt = cta - mt * N_NT;
+            if (tid < W1_ACTIVE) {
+                const int m = tid / (NT / 4), n4b = tid - m * (NT / 4);
+                const int off = DDPM_OFF_W1 + (mt * MT + m) * IN + nt * NT + n4b * 4;
+                float g[4] = {contrib(off, step), contrib(off + 1, step), contrib(off + 2, step), contrib(off + 3, step)};
+                ll_allreduce<4>(a, T, home_w1, off, g);
+                if (last) *reinterpret_cast<float4*>(a.xout + off) = make_float4(g[0], g[1], g[2], g[3]);
+            } else if (nt == 0 && tid < W1_ACTIVE + MT) {
+                const int offb = DDPM_OFF_B1 + mt * MT + (tid - W1_ACTIVE);
+                float gb[1] = {contrib(offb, step)};
+                ll_allreduce<1>(a, T, (tid - W1_ACTIVE) % a.world, offb, gb);
+                if (last) a.xout[offb] = gb[0];
+            }
+        } else if (cta < CTA_W3) {
+            const int t2 = cta - CTA_W2, jt = t2 >> 2, kt = t2 & 3, jj = tid >> 4, k2 = tid & 15;
+            const int off = DDPM_OFF_W2 + (jt * 16 + jj) * HID + kt * 32 + k2 * 2;
+            float g[2] = {contrib(off, step), contrib(off + 1, step)};
+            ll_allreduce<2>(a, T, home_sm, off, g);
+            if (last) { a.xout[off] = g[0]; a.xout[off + 1] = g[1]; }
+            if (kt == 0 && tid < 16) {
+                const int offb = DDPM_OFF_B2 + jt * 16 + tid;
+                float gb[1] = {contrib(offb, step)};
+                ll_allreduce<1>(a, T, tid % a.world, offb, gb);
+                if (last) a.xout[offb] = gb[0];
+            }
+        } else {
+            const int kt = cta - CTA_W3, k = tid & 31, c0 = tid >> 5, c1 = c0 + 8;
+            const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
+            float ga[1] = {contrib(o0, step)};
+            ll_allreduce<1>(a, T, home_sm, o0, ga);
+            if (last) a.xout[o0] = ga[0];
+            if (c1 < NC) {
+                float gc[1] = {contrib(o1, step)};
+                ll_allreduce<1>(a, T, home_sm, o1, gc);
+                if (last) a.xout[o1] = gc[0];
+            }
         }
     }
 }
@@ -1004,11 +1078,12 @@ static int persist_fill_and_launch(PersistArgs& a, float* d_params, float* d_gra
     a.B = batch; a.nsteps = nsteps; a.gscale = grad_scale; a.lr = lr;
     a.train = ((flags & DDPM_FWD_PHILOX_MASK) || d_masks != nullptr) ? 1 : 0;
     a.loss2 = d_loss; a.loss_steps = d_loss_steps;
-    a.part = (float*)(ws + L.part1);
-    a.h1d = (float*)(ws + L.h1d); a.h2 = (float*)(ws + L.h2);
-    a.dz2 = (float*)(ws + L.dz2); a.dz1 = (float*)(ws + L.dz1);
-    a.dz3 = (float*)(ws + L.dz3); a.rowloss = (float*)(ws + L.rowloss);
-    a.bar = (unsigned long long*)(ws + L.ctrl) + 2;     // ctrl words 4..7
+    a.llpart = (unsigned long long*)(ws + L.ll_part);
+    a.llact = (unsigned long long*)(ws + L.ll_act);
+    a.llloss = (unsigned long long*)(ws + L.ll_loss);
+    a.llb1 = (unsigned long long*)(ws + L.ll_b1);
+    a.ctl = (unsigned long long*)(ws + L.ctrl);
+    a.lerr = (int*)(ws + L.ctrl) + CTRL_ERR32;
     a.dbg = g_persist_dbg;
     void* kargs[] = {&a};
     const bool feed = a.feed_flags != nullptr, ddp = a.world > 1;
@@ -1088,7 +1163,7 @@ extern "C" int ddpm_comm_create(int rank, int world, ddpm_comm** out) {
     }
     DDPM_CUDA(cudaGetDevice(&c->device));
     c->recv_bytes = 2 * (size_t)world * NP * sizeof(unsigned long long);     // 15 MB at world 8
-    c->dz_bytes = 2 * (size_t)world * CR * ACT_ROW_WORDS * sizeof(unsigned long long);      // 4.3 MB at world 8
+    c->dz_bytes = 2 * (size_t)world * CR * XACT_ROW_WORDS * sizeof(unsigned long long);     // 1 MB at world 8
     cudaError_t e = cudaMalloc(&c->local, c->recv_bytes + c->dz_bytes + 256);
     if (e != cudaSuccess) { delete c; return set_error("ddpm_comm_create: cudaMalloc failed: %s", cudaGetErrorString(e)); }
     e = cudaMemset(c->local, 0, c->recv_bytes + c->dz_bytes + 256);   // step field 0 never matches a real step (steps start at 1)
@@ -1165,7 +1240,6 @@ extern "C" int ddpm_train_steps_fused_ddp(
     //  multiplies ws x 64 rows of pixels per tile, which outweighs the saved traffic beyond 4 ranks; DDPM_ACT_EXCHANGE=1 forces it)
     const bool act_default = comm->world <= 4 || getenv("DDPM_ACT_EXCHANGE") != nullptr;
     a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && act_default && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
-    if (a.act_exchange && getenv("DDPM_ACT_EXCHANGE_ALL") != nullptr) a.act_exchange = 2;   // also W2 / W3 / biases (measured slower at ws = 2)
     a.idx_all = d_idx_all; a.idx_stride = (size_t)idx_stride;
     if (d_idx == nullptr && d_idx_all != nullptr) d_idx = d_idx_all + (size_t)comm->rank * idx_stride;
     const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,
@@ -1173,6 +1247,29 @@ extern "C" int ddpm_train_steps_fused_ddp(
                                            d_loss, d_loss_steps, d_workspace, stream, "ddpm_train_steps_fused_ddp");
     if (rc == 0) comm->steps += (unsigned long long)nsteps;
     return rc;
+}
+
+extern "C" int ddpm_comm_exchange_only(ddpm_comm* comm, int nsteps, float* d_out, void* stream) {
+    DDPM_CHECK_ARG(comm != nullptr && comm->world > 1, "ddpm_comm_exchange_only: needs a communicator of world > 1");
+    DDPM_CHECK_ARG(nsteps > 0, "ddpm_comm_exchange_only: nsteps must be positive (got %d)", nsteps);
+    DDPM_CHECK_ARG(((uintptr_t)d_out & 15) == 0, "ddpm_comm_exchange_only: d_out must be 16-byte aligned");
+    for (int r = 0; r < comm->world; ++r)
+        DDPM_CHECK_ARG(comm->peer[r] != nullptr, "ddpm_comm_exchange_only: rank %d is not connected (ddpm_comm_connect)", r);
+    PersistArgs a;
+    memset(&a, 0, sizeof(a));
+    comm_fill(a, comm);
+    a.nsteps = nsteps; a.xout = d_out;
+    void* kargs[] = {&a};
+    DDPM_CUDA(cudaLaunchCooperativeKernel((const void*)exchange_only_kernel, dim3(P_GRID), dim3(P_THREADS), kargs, 0,
+                                          (cudaStream_t)stream));
+    comm->steps += (unsigned long long)nsteps;
+    return 0;
+}
+
+extern "C" int ddpm_workspace_error(const void* d_workspace, int* h_err) {
+    DDPM_CHECK_ARG(d_workspace && h_err, "ddpm_workspace_error: null argument");
+    DDPM_CUDA(cudaMemcpy(h_err, (const int*)d_workspace + CTRL_ERR32, sizeof(int), cudaMemcpyDeviceToHost));
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------------

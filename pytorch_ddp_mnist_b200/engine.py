@@ -107,8 +107,11 @@ class TrainEngine:
         return False
 
     def check_comm(self) -> None:
+        """Blocking.  Raises if a wait inside the step kernel gave up (a peer that never showed up, ~3 s bound)."""
         if self.comm is not None and self.comm.error():
             raise RuntimeError("fused data-parallel step: a peer did not show up within the exchange timeout")
+        if self.ws.error():
+            raise RuntimeError("persistent step kernel: a wait for another block's data timed out (results invalid)")
 
     # ------------------------------------------------------------------ steps
     def train_step(self, resident, idx: torch.Tensor, mask: Optional[torch.Tensor] = None,

@@ -88,6 +88,13 @@ class Workspace:
     def nbytes(self) -> int:
         return self.buf.numel()
 
+    def error(self) -> int:
+        """Non-zero once a wait inside the persistent kernel gave up (~3 s): see ddpm_workspace_error.  Blocking."""
+        import ctypes as C
+        e = C.c_int(0)
+        check(lib.ddpm_workspace_error(ptr(self.buf), C.byref(e)))
+        return e.value
+
 
 def step_forward(params: torch.Tensor, ws: Workspace, batch: int, *,
                  images: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None,
@@ -167,6 +174,12 @@ def train_steps_persistent(params: torch.Tensor, ws: Workspace, batch: int, nste
     check(lib.ddpm_train_steps_persistent(ptr(params), ptr(grads), ptr(images), ptr(labels), n, ptr(idx),
                                           ptr(masks), seed, step0, batch, nsteps, flags, grad_scale, lr,
                                           ptr(loss), ptr(loss_steps), ptr(ws.buf), cur_stream()))
+
+
+def exchange_only(comm: "FusedComm", nsteps: int, out: Optional[torch.Tensor] = None) -> None:
+    """The fused step's gradient exchange alone, `nsteps` times (measurement / test aid, collective)."""
+    _need(out, "out", torch.float32, (N_PARAMS,), optional=True)
+    check(lib.ddpm_comm_exchange_only(comm._h, int(nsteps), ptr(out), cur_stream()))
 
 
 def launch_floor(nlaunches: int = 1) -> None:

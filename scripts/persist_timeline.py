@@ -25,21 +25,28 @@ ops.train_steps_persistent(eng.params, eng.ws, B, 20, images=images, labels=labe
 torch.cuda.synchronize()
 _lib.lib.ddpm_debug_set_persist_timing(None)
 d = dbg.cpu().numpy().reshape(G, 8, 16)
-names = ["phaseA", "wait1", "phaseB", "wait2", "phaseC"]
+# stamps: 0 step start | 1 phase A done (partials stored) | 2 first row's partials arrived (row CTAs) | 3 phase B done
+#         4 first operands of phase C arrived | 5 phase C done.  Non-row CTAs have no stamp 2 (3 follows 1 directly).
 print("cycles per segment, averaged over steps 2..7 (clock64, ~1.9 GHz)")
+def seg(cta, a, b):
+    return int((d[cta, 2:8, b] - d[cta, 2:8, a]).mean())
 for cta in (0, 1, 63, 64, 100, 111, 112, 130, 143, 144, 145, 146, 147):
-    seg = (d[cta, 2:8, 1:6] - d[cta, 2:8, 0:5]).mean(axis=0)
-    tot = (d[cta, 3:8, 0] - d[cta, 2:7, 0]).mean()
-    print(f"cta {cta:3d}: " + " ".join(f"{n}={int(v):6d}" for n, v in zip(names, seg)) + f"  step={int(tot)}")
-seg_all = (d[:, 2:8, 1:6] - d[:, 2:8, 0:5]).mean(axis=1)
-print("max over CTAs:", dict(zip(names, seg_all.max(axis=0).astype(int))))
-print("mean over CTAs:", dict(zip(names, seg_all.mean(axis=0).astype(int))))
-
-# finer stamps: phase B of a row CTA (2 -> 6 staged+partials, 6 -> 7 h1d+z2, 7 -> 8 logits+softmax, 8 -> 3 dz2+dz1)
+    tot = int((d[cta, 3:8, 0] - d[cta, 2:7, 0]).mean())
+    row = cta < B
+    if row:
+        print(f"cta {cta:3d}: A={seg(cta,0,1):6d} wait_partials={seg(cta,1,2):6d} B={seg(cta,2,3):6d} "
+              f"wait_rows={seg(cta,3,4):6d} C={seg(cta,4,5):6d}  step={tot}")
+    else:
+        print(f"cta {cta:3d}: A={seg(cta,0,1):6d} {'':21s} (idle)={seg(cta,1,3):6d} "
+              f"wait_rows={seg(cta,3,4):6d} C={seg(cta,4,5):6d}  step={tot}")
 for cta in (0, 63):
     x = d[cta, 2:8]
-    print(f"cta {cta} phase B: partials+wait={int((x[:,6]-x[:,2]).mean())} z2={int((x[:,7]-x[:,6]).mean())} "
-          f"logits+softmax={int((x[:,8]-x[:,7]).mean())} dz2+dz1={int((x[:,3]-x[:,8]).mean())}")
+    print(f"cta {cta} phase B: z1+h1d={int((x[:,7]-x[:,6]).mean())} (incl. z2) logits+softmax+dz2={int((x[:,8]-x[:,7]).mean())} dz1={int((x[:,3]-x[:,8]).mean())}")
+for cta in (0, 1, 63):
+    x = d[cta, 3:8]
+    f = lambda k: int((x[:, k] - x[:, 0]).mean())
+    print(f"cta {cta} (cycles into the step): A done {f(1)}, W2/W3 loads issued {f(13)}, past the ready check {f(14)}, "
+          f"partials polled {f(15)}, b1 polled {f(12)}, first barrier of phase B {f(2)}")
 for cta in (0, 100):
     x = d[cta, 2:8]
-    print(f"cta {cta} phase C: load+sync={int((x[:,9]-x[:,4]).mean())} loop={int((x[:,10]-x[:,9]).mean())} update={int((x[:,5]-x[:,10]).mean())}")
+    print(f"cta {cta} phase C: loop={int((x[:,10]-x[:,9]).mean())} update={int((x[:,5]-x[:,10]).mean())}")

@@ -33,13 +33,21 @@ _lib.lib.ddpm_debug_set_persist_timing(None)
 eng.check_comm()
 d = dbg.cpu().numpy().reshape(G, 8, 16)
 if rank == 0:
-    names = ["phaseA", "wait1", "phaseB", "wait2", "phaseC"]
+    def seg(cta, a_, b_):
+        return int((d[cta, 2:8, b_] - d[cta, 2:8, a_]).mean())
+    print(f"world {world}: cycles per segment, averaged over steps 2..7 of a 20-step launch (rank 0)")
     for cta in (0, 63, 64, 111, 112, 146):
-        seg = (d[cta, 2:8, 1:6] - d[cta, 2:8, 0:5]).mean(axis=0)
-        tot = (d[cta, 3:8, 0] - d[cta, 2:7, 0]).mean()
-        print(f"cta {cta:3d}: " + " ".join(f"{n}={int(v):6d}" for n, v in zip(names, seg)) + f"  step={int(tot)}")
+        tot = int((d[cta, 3:8, 0] - d[cta, 2:7, 0]).mean())
+        if cta < B:
+            print(f"cta {cta:3d}: A={seg(cta,0,1):6d} wait_partials={seg(cta,1,2):6d} B={seg(cta,2,3):6d} "
+                  f"wait_rows={seg(cta,3,4):6d} C={seg(cta,4,5):6d}  step={tot}")
+        else:
+            print(f"cta {cta:3d}: A={seg(cta,0,1):6d} (idle)={seg(cta,1,3):6d} wait_rows={seg(cta,3,4):6d} "
+                  f"C={seg(cta,4,5):6d}  step={tot}")
     for cta in (0, 100):
         x = d[cta, 2:8]
-        print(f"cta {cta} phase B: partials+wait={int((x[:,6]-x[:,2]).mean())} z2={int((x[:,7]-x[:,6]).mean())} logits+softmax={int((x[:,8]-x[:,7]).mean())} dz2+dz1={int((x[:,3]-x[:,8]).mean())}")
+        if (x[:, 12] > 0).all():
+            print(f"cta {cta} phase C: gradient tile ready after {int((x[:,11]-x[:,4]).mean())}, "
+                  f"exchange (push + wait + sum) {int((x[:,12]-x[:,11]).mean())}, update {int((x[:,5]-x[:,12]).mean())}")
 dist.barrier()
 os._exit(0)

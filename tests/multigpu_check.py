@@ -69,6 +69,32 @@ def check_ddp_wrapped_model(rank, world, local, dev, g):
     return float(err)
 
 
+def check_exchange_only(rank, world, dev):
+    """The fused step's gradient exchange alone, both algorithms (one-shot: everyone pushes to everyone; two-stage:
+    thread slices have a home rank that sums and pushes back), over three launches on one communicator: every
+    element of the bucket must come out as the exact sum of the ranks' contributions, identically on all ranks."""
+    from pytorch_ddp_mnist_b200 import ops
+    e = np.arange(O.N_PARAMS)
+    unit = (1 + (e & 1023)).astype(np.float64) / 1024.0
+    for algo in ("one_shot", "two_stage"):
+        os.environ["DDPM_EXCHANGE"] = algo
+        try:
+            comm = ops.FusedComm(rank, world)
+        finally:
+            os.environ.pop("DDPM_EXCHANGE", None)
+        out = torch.zeros(O.N_PARAMS, device=dev)
+        for nsteps in (1, 6, 3):
+            out.fill_(-1.0)
+            ops.exchange_only(comm, nsteps, out)
+            torch.cuda.synchronize()
+            assert comm.error() == 0, (algo, "exchange timed out")
+            want = unit * (world * (world + 1) / 2) + world * ((nsteps - 1) & 255)
+            got = out.cpu().numpy().astype(np.float64)
+            assert np.array_equal(got, want), (algo, nsteps, int((got != want).sum()), got[:4], want[:4])
+        dist.barrier()
+        comm.close()
+
+
 def check_slab_loader(rank, world, dev):
     """`ResidentDataset.from_file` at ws > 1: every rank reads one contiguous slab of the CDF-5 file and an
     all-gather replicates the u8 dataset - the result must be the file's bytes on every rank."""
@@ -99,6 +125,17 @@ def main():
     assert rec["ok"], rec
     if world in parity_gate.GOLDEN_WS:
         assert rec["golden"] and rec["max_loss_err"] is not None
+
+    if world == 2:
+        # two ranks default to the one-shot exchange: run the gate once more through the two-stage algorithm (the
+        # default beyond 2 ranks), so that a 2-GPU box checks it against the reference as well
+        os.environ["DDPM_EXCHANGE"] = "two_stage"
+        try:
+            rec2 = parity_gate.run_gate(dev, rank, world, dist, include_host_fed=False)
+        finally:
+            os.environ.pop("DDPM_EXCHANGE", None)
+        assert rec2["ok"], rec2
+    check_exchange_only(rank, world, dev)
 
     im, lb = synth.synth(synth.TRAIN_N, synth.TRAIN_SEED)
     res = ResidentDataset.from_arrays(im, lb, dev)

@@ -21,7 +21,7 @@ TOL_F32 = 2e-5          # same bound the other GPU parity tests use
 def test_static_scratch_covers_its_stated_limit():
     """CPU-side: the built-in array (3,490,816 B) is large enough for the stated 128-row limit."""
     from pytorch_ddp_mnist_b200 import _lib
-    assert _lib.lib.ddpm_workspace_bytes(_lib.STATIC_SCRATCH_MAX_BATCH) <= 3490816
+    assert _lib.lib.ddpm_workspace_forward_bytes(_lib.STATIC_SCRATCH_MAX_BATCH) <= 3490816
 
 
 @pytest.mark.gpu
