@@ -241,29 +241,38 @@ __device__ __forceinline__ void ll_store(unsigned long long* dst, unsigned t32, 
 __device__ __forceinline__ void ll_store1(unsigned long long* dst, unsigned t32, float v) {
     asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"(__float_as_uint(v)), "r"(t32) : "memory");
 }
+// N tagged words at src (N == 1, or even N read as 16-byte pairs): all loads in flight at once, then only what has
+// not arrived is re-polled (a dependent round trip per word made a 4-word poll cost 2 L2 round trips even when
+// everything had arrived).
+template <int N>
+__device__ __forceinline__ void ll_load(const unsigned long long* src, unsigned (&x)[N], unsigned (&f)[N]) {
+    if (N == 1) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x[0]), "=r"(f[0]) : "l"(src) : "memory");
+    } else {
+#pragma unroll
+        for (int i = 0; i < N; i += 2)
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x[i]), "=r"(f[i]), "=r"(x[i + (N > 1 ? 1 : 0)]),
+                         "=r"(f[i + (N > 1 ? 1 : 0)]) : "l"(src + i) : "memory");
+    }
+}
+template <int N>
+__device__ __forceinline__ bool ll_missing(const unsigned (&f)[N], unsigned t32) {
+    bool m = false;
+#pragma unroll
+    for (int i = 0; i < N; ++i) m |= f[i] != t32;
+    return m;
+}
 template <int N>
 __device__ __forceinline__ void ll_poll(int* err, const unsigned long long* src, unsigned t32, long long t0,
                                         float (&got)[N]) {
-    unsigned spins = 0;
-    if (N == 1) {
-        unsigned x, f;
-        for (;;) {
-            asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
-            if (f == t32 || poll_miss(err, t0, spins)) break;
-        }
-        got[0] = __uint_as_float(x);
-    } else {
-#pragma unroll
-        for (int i = 0; i < N; i += 2) {
-            unsigned x0, f0, x1, f1;
-            for (;;) {
-                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(f0), "=r"(x1), "=r"(f1)
-                             : "l"(src + i) : "memory");
-                if ((f0 == t32 && f1 == t32) || poll_miss(err, t0, spins)) break;
-            }
-            got[i] = __uint_as_float(x0); got[i + (N > 1 ? 1 : 0)] = __uint_as_float(x1);
-        }
+    unsigned x[N], f[N], spins = 0;
+    ll_load<N>(src, x, f);
+    while (ll_missing<N>(f, t32)) {
+        if (poll_miss(err, t0, spins)) break;
+        ll_load<N>(src, x, f);
     }
+#pragma unroll
+    for (int i = 0; i < N; ++i) got[i] = __uint_as_float(x[i]);
 }
 // Cross-GPU all-reduce of this thread's N gradient values.  v: this rank's contribution on entry, the sum over all
 // ranks (rank order) on exit.
@@ -273,42 +282,70 @@ __device__ __forceinline__ void ll_poll(int* err, const unsigned long long* src,
 //             Homes are spread over the threads of every CTA (thread slices of a tile), so on every rank every SM
 //             sends and receives the same share (round 1 made whole CTAs home: 14 SMs per rank did all the summing).
 // All pushes of a thread come before any of its waits, so diverged lanes of a warp never wait for each other.
+// The summing thread has the words of ALL sources in flight at once and re-polls only the missing ones: the wait is
+// one L2 round trip after the last source arrived, not one per source.
+// Split in two so that a thread with several exchanges (a tile and a bias, two classes of W3) has all of them on the
+// wire before it waits for any: ll_ar_begin = this thread's first-hop pushes, ll_ar_end = everything else.
 template <int N>
-__device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
+__device__ __forceinline__ void ll_ar_begin(const PersistArgs& a, unsigned long long T, int home, int off, const float (&v)[N]) {
+    const unsigned t32 = (unsigned)T;
+    const size_t par = (size_t)(T & 1) * a.world;
+    if (a.two_stage) {
+        if (home != a.rank) ll_store<N>(a.xrecv[home] + (par + a.rank) * NP + off, t32, v);
+    } else {
+        for (int r = 0; r < a.world; ++r)
+            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
+    }
+}
+template <int N>
+__device__ __forceinline__ void ll_ar_end(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
     const unsigned t32 = (unsigned)T;
     const size_t par = (size_t)(T & 1) * a.world;
     const long long t0 = clock64();
     const bool is_home = !a.two_stage || home == a.rank;
     if (!is_home) {
-        ll_store<N>(a.xrecv[home] + (par + a.rank) * NP + off, t32, v);
-    } else if (!a.two_stage) {
-        for (int r = 0; r < a.world; ++r)
-            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
-    }
-    if (is_home) {
-        // (polling every source at once before summing was tried: the extra live registers spill in the 255-register
-        //  kernel and the step got slower at 2 and 4 GPUs: 10.97 -> 8.94 M, 15.7 -> 13.3 M img/s)
-        float sum[N];
-        for (int r = 0; r < a.world; ++r) {
-            float got[N];
-            if (r == a.rank) {
-#pragma unroll
-                for (int i = 0; i < N; ++i) got[i] = v[i];
-            } else {
-                ll_poll<N>(a.xerr, a.xrecv[a.rank] + (par + r) * NP + off, t32, t0, got);
-            }
-#pragma unroll
-            for (int i = 0; i < N; ++i) sum[i] = (r == 0) ? got[i] : sum[i] + got[i];
-        }
-        if (a.two_stage) {
-            for (int r = 0; r < a.world; ++r)
-                if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
-        }
-#pragma unroll
-        for (int i = 0; i < N; ++i) v[i] = sum[i];
-    } else {
         ll_poll<N>(a.xerr, a.xrecv[a.rank] + (par + home) * NP + off, t32, t0, v);
+        return;
     }
+    const unsigned long long* mine = a.xrecv[a.rank] + par * NP + off;
+    unsigned x[DDPM_MAX_WORLD][N], f[DDPM_MAX_WORLD][N], spins = 0;
+#pragma unroll
+    for (int r = 0; r < DDPM_MAX_WORLD; ++r) {
+        if (r < a.world && r != a.rank) ll_load<N>(mine + (size_t)r * NP, x[r], f[r]);
+        else {
+#pragma unroll
+            for (int i = 0; i < N; ++i) { x[r][i] = __float_as_uint(v[i]); f[r][i] = t32; }
+        }
+    }
+    for (;;) {
+        bool missing = false;
+#pragma unroll
+        for (int r = 0; r < DDPM_MAX_WORLD; ++r) missing |= ll_missing<N>(f[r], t32);
+        if (!missing || poll_miss(a.xerr, t0, spins)) break;
+#pragma unroll
+        for (int r = 0; r < DDPM_MAX_WORLD; ++r)
+            if (ll_missing<N>(f[r], t32)) ll_load<N>(mine + (size_t)r * NP, x[r], f[r]);
+    }
+    float sum[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) sum[i] = __uint_as_float(x[0][i]);
+#pragma unroll
+    for (int r = 1; r < DDPM_MAX_WORLD; ++r)
+        if (r < a.world) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) sum[i] += __uint_as_float(x[r][i]);
+        }
+    if (a.two_stage) {
+        for (int r = 0; r < a.world; ++r)
+            if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = sum[i];
+}
+template <int N>
+__device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
+    ll_ar_begin<N>(a, T, home, off, v);
+    ll_ar_end<N>(a, T, home, off, v);
 }
 
 // dst[r][0..NCOLS) for rows r < CR from tagged words at base[r * row_stride + c] (polled until they carry tag
@@ -851,15 +888,17 @@ train_persist_kernel(PersistArgs a) {
                 for (int q = 0; q < 4; ++q) p[q] = *reinterpret_cast<const float2*>(&pb[(q * 16 + jj) * 32 + k2 * 2]);
                 float g[2] = {((p[0].x + p[1].x) + (p[2].x + p[3].x)) * a.gscale,
                               ((p[0].y + p[1].y) + (p[2].y + p[3].y)) * a.gscale};
-                if (ddp) ll_allreduce<2>(a, T, home_sm, off, g);
-                grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
-                grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
-            }
-            if (do_db) {
                 const int offb = DDPM_OFF_B2 + jt * 16 + tid;
                 float gb[1] = {db_acc * a.gscale};
-                if (ddp) ll_allreduce<1>(a, T, tid % a.world, offb, gb);
-                grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
+                if (ddp) {                                       // tile and bias on the wire before either wait
+                    ll_ar_begin<2>(a, T, home_sm, off, g);
+                    if (do_db) ll_ar_begin<1>(a, T, tid % a.world, offb, gb);
+                    ll_ar_end<2>(a, T, home_sm, off, g);
+                    if (do_db) ll_ar_end<1>(a, T, tid % a.world, offb, gb);
+                }
+                grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
+                grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
+                if (do_db) grad_out(a.grads, a.lr, a.params, offb, gb[0], pbias);
             }
         } else {
             // ---- dW3 column tile [10 classes][32 cols].  thread -> (batch eighth bq, column k), all 10 classes:
@@ -913,16 +952,19 @@ train_persist_kernel(PersistArgs a) {
 #pragma unroll
                 for (int q = 0; q < 8; ++q) g0 += pb[(q * NC + c0) * 32 + k];
                 const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
-                float ga[1] = {g0 * a.gscale};
-                if (ddp) ll_allreduce<1>(a, T, home_sm, o0, ga);
-                grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) {
 #pragma unroll
                     for (int q = 0; q < 8; ++q) g1 += pb[(q * NC + c1) * 32 + k];
-                    float gc[1] = {g1 * a.gscale};
-                    if (ddp) ll_allreduce<1>(a, T, home_sm, o1, gc);
-                    grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
                 }
+                float ga[1] = {g0 * a.gscale}, gc[1] = {g1 * a.gscale};
+                if (ddp) {                                       // both classes on the wire before either wait
+                    ll_ar_begin<1>(a, T, home_sm, o0, ga);
+                    if (c1 < NC) ll_ar_begin<1>(a, T, home_sm, o1, gc);
+                    ll_ar_end<1>(a, T, home_sm, o0, ga);
+                    if (c1 < NC) ll_ar_end<1>(a, T, home_sm, o1, gc);
+                }
+                grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
+                if (c1 < NC) grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
             }
             if (kt == 2 && warp == 0) {
                 // batch loss: 256 strided partial sums -> 32 lanes (fixed order) -> shuffle tree
@@ -997,25 +1039,25 @@ exchange_only_kernel(PersistArgs a) {
             const int t2 = cta - CTA_W2, jt = t2 >> 2, kt = t2 & 3, jj = tid >> 4, k2 = tid & 15;
             const int off = DDPM_OFF_W2 + (jt * 16 + jj) * HID + kt * 32 + k2 * 2;
             float g[2] = {contrib(off, step), contrib(off + 1, step)};
-            ll_allreduce<2>(a, T, home_sm, off, g);
+            const bool do_db = kt == 0 && tid < 16;
+            const int offb = DDPM_OFF_B2 + jt * 16 + tid;
+            float gb[1] = {contrib(offb, step)};
+            ll_ar_begin<2>(a, T, home_sm, off, g);
+            if (do_db) ll_ar_begin<1>(a, T, tid % a.world, offb, gb);
+            ll_ar_end<2>(a, T, home_sm, off, g);
+            if (do_db) ll_ar_end<1>(a, T, tid % a.world, offb, gb);
             if (last) { a.xout[off] = g[0]; a.xout[off + 1] = g[1]; }
-            if (kt == 0 && tid < 16) {
-                const int offb = DDPM_OFF_B2 + jt * 16 + tid;
-                float gb[1] = {contrib(offb, step)};
-                ll_allreduce<1>(a, T, tid % a.world, offb, gb);
-                if (last) a.xout[offb] = gb[0];
-            }
+            if (last && do_db) a.xout[offb] = gb[0];
         } else {
             const int kt = cta - CTA_W3, k = tid & 31, c0 = tid >> 5, c1 = c0 + 8;
             const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
-            float ga[1] = {contrib(o0, step)};
-            ll_allreduce<1>(a, T, home_sm, o0, ga);
+            float ga[1] = {contrib(o0, step)}, gc[1] = {contrib(o1, step)};
+            ll_ar_begin<1>(a, T, home_sm, o0, ga);
+            if (c1 < NC) ll_ar_begin<1>(a, T, home_sm, o1, gc);
+            ll_ar_end<1>(a, T, home_sm, o0, ga);
+            if (c1 < NC) ll_ar_end<1>(a, T, home_sm, o1, gc);
             if (last) a.xout[o0] = ga[0];
-            if (c1 < NC) {
-                float gc[1] = {contrib(o1, step)};
-                ll_allreduce<1>(a, T, home_sm, o1, gc);
-                if (last) a.xout[o1] = gc[0];
-            }
+            if (last && c1 < NC) a.xout[o1] = gc[0];
         }
     }
 }
