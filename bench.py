@@ -420,7 +420,7 @@ def main() -> None:
     kern = _time_kernels(torch, ops, eng, resident, shard_dev, B, world)
 
     # ---- e2e: host buffers in, loss out, every step
-    e2e = _time_e2e(torch, eng, im, lb, shard, B, max(min(K * 10, 2000), 200), world, dev, dist if world > 1 else None)
+    e2e = _time_e2e(torch, eng, im, lb, shard, B, 2000, world, dev, dist if world > 1 else None)
 
     context = None
     if not args.no_context:

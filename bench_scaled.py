@@ -27,10 +27,25 @@ import threading
 import time
 
 
-def _make_file(path: str, n: int, seed: int) -> float:
+def _part_worker(path, n, seed, part, nparts):
     from pytorch_ddp_mnist_b200 import synth
+    synth.write_synth_file_part(path, n, seed, part, nparts, False)
+
+
+def _make_file(path: str, n: int, seed: int, part: int = 0, nparts: int = 1, procs: int = 0) -> float:
+    """This process's share (part of nparts) of the file, written by `procs` worker processes (chunks are independent).
+    The header must exist already (write_synth_file_part(create=True))."""
+    import multiprocessing as mp
     t0 = time.perf_counter()
-    synth.write_synth_file(path, n, seed)
+    procs = procs or max(1, min(16, (os.cpu_count() or 8) // max(nparts, 1)))
+    ctx = mp.get_context("fork")
+    ws = [ctx.Process(target=_part_worker, args=(path, n, seed, part * procs + k, nparts * procs)) for k in range(procs)]
+    for w in ws:
+        w.start()
+    for w in ws:
+        w.join()
+        if w.exitcode != 0:
+            raise RuntimeError("synthetic file writer failed")
     return time.perf_counter() - t0
 
 
@@ -79,18 +94,25 @@ def run(args, clock_sampler_cls, metric) -> None:
         dist.init_process_group("nccl", init_method="env://", device_id=dev)
         dd = dist
 
-    # ---- the file: written once by rank 0 (synthetic generator of SURVEY.md §8(d), seed 1234, CDF-5)
-    box = [None, 0.0]
+    # ---- the file (synthetic generator of SURVEY.md §8(d), seed 1234, CDF-5): rank 0 lays it out, then every rank
+    #      writes its share of the 100,000-sample chunks with a few worker processes (chunks have independent generators)
+    box = [None, False]
     if rank == 0:
         d = os.environ.get("DDPM_SCALED_DIR") or tempfile.mkdtemp(prefix="scaled6m_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
         path = os.path.join(d, "mnist_train_images.nc")
-        gen_s = 0.0
-        if not os.path.exists(path):
-            gen_s = _make_file(path, n, 1234)
-        box = [path, gen_s]
+        fresh = not os.path.exists(path)
+        if fresh:
+            from pytorch_ddp_mnist_b200 import synth
+            synth.write_synth_file_part(path, n, 1234, 0, 1, True)
+        box = [path, fresh]
     if world > 1:
         dist.broadcast_object_list(box, src=0)
-    path, gen_s = box
+    path, fresh = box
+    gen_s = 0.0
+    if fresh:
+        gen_s = _make_file(path, n, 1234, rank, world)
+        if world > 1:
+            dist.barrier()
     file_bytes = os.path.getsize(path)
 
     # ---- loader: first load (page cache as the writer left it), second load (warm)
@@ -259,6 +281,8 @@ def _reference_arm(args, n, metric):
     d = os.environ.get("DDPM_SCALED_DIR") or tempfile.mkdtemp(prefix="scaled6m_ref_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     path = os.path.join(d, "mnist_train_images.nc")
     if not os.path.exists(path):
+        from pytorch_ddp_mnist_b200 import synth
+        synth.write_synth_file_part(path, n, 1234, 0, 1, True)
         _make_file(path, n, 1234)
     ws = max(2, args.gpus)
     steps = max(1, min(args.steps, 300))

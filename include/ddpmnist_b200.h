@@ -122,6 +122,13 @@ int ddpm_step_forward(const float* d_params,
  * flags: DDPM_BWD_TF32 computes fc1's weight gradient dW1 = dz1^T . X with tcgen05 TF32 tensor-core MMAs
  * (batch >= 2048 and the resident uint8 dataset path only; ignored otherwise); ~1e-3 relative. */
 #define DDPM_BWD_TF32 1u
+/* Two-part backward (batch >= 1024, data-parallel runs): DDPM_BWD_PART_SMALL computes everything except fc1's weight
+ * gradient (bucket elements 100352..118271: b1, W2, b2, W3), DDPM_BWD_PART_W1 computes only fc1's weight gradient
+ * (elements 0..100351).  Called in that order they equal one plain call, and the all-reduce of the small part (71,680 B)
+ * can run while the second call computes - the overlap of the bucket all-reduce with backward that
+ * DistributedDataParallel's hooks give the reference (mp:439, 462). */
+#define DDPM_BWD_PART_SMALL 2u
+#define DDPM_BWD_PART_W1 4u
 int ddpm_step_backward(float* d_params,
                        const uint8_t* d_images, int64_t n_samples,
                        const int64_t* d_idx, const float* d_x,

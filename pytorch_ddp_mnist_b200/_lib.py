@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("DDPM_LIB") or os.path.join(_HERE, "libddpmnist_b200.s
 IN, HID, CLASSES, N_PARAMS = 784, 128, 10, 118272
 OFF_W1, OFF_B1, OFF_W2, OFF_B2, OFF_W3 = 0, 100352, 100480, 116864, 116992
 FWD_PREP_BACKWARD, FWD_PHILOX_MASK, FWD_TF32 = 1, 2, 4
-BWD_TF32 = 1
+BWD_TF32, BWD_PART_SMALL, BWD_PART_W1 = 1, 2, 4
 CN_BWD_TRAIN, CN_BWD_TF32, CN_BWD_FWD_WAS_TF32 = 1, 2, 4
 STATIC_SCRATCH_MAX_BATCH = 128
 PERSIST_MAX_BATCH = 512

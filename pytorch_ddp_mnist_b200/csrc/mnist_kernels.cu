@@ -805,6 +805,7 @@ struct GradArgs {
     const float* h1d; const float* h2; const float* dz1; const float* dz2; const float* dz3;
     int B; float scale, lr;
     int bsplit_w1, skip_w1;            // dW1 comes from the tensor-core kernel (its own slice count); grads_kernel skips it
+    int skip_small;                    // only dW1 (DDPM_BWD_PART_W1): the other items were done by an earlier call
     int bsplit; float* gpart;          // large batches: the batch is cut in bsplit slices, raw partial gradients [bsplit][NP]
 };
 
@@ -938,6 +939,7 @@ grads_kernel(GradArgs a) {
     for (int work = blockIdx.x; work < GRAD_ITEMS * a.bsplit; work += gridDim.x) {
         const int bs = work / GRAD_ITEMS, item = work - bs * GRAD_ITEMS;
         const int b0 = bs * slice, b1 = min(a.B, b0 + slice);
+        if (item >= N_GW1 && a.skip_small) continue;
         if (item < N_GW1) {
             if (a.skip_w1) continue;
             if (a.bsplit > 1) {
@@ -982,8 +984,9 @@ grads_kernel(GradArgs a) {
 // Combine the batch slices' partial gradients in fixed order, scale, write the bucket and/or apply SGD.
 __global__ void __launch_bounds__(256)
 grads_finalize_kernel(GradArgs a) {
-    const int n4 = NP / 4;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
+    // range of the bucket this launch finalises: all of it, only fc1's weights, or everything behind them
+    const int lo4 = a.skip_w1 == 2 ? DDPM_OFF_B1 / 4 : 0, n4 = a.skip_small ? DDPM_OFF_B1 / 4 : NP / 4;
+    for (int i = lo4 + blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
         float4 g = __ldcg(reinterpret_cast<const float4*>(a.gpart) + i);
         const int nsl = (i * 4 < DDPM_OFF_B1) ? a.bsplit_w1 : a.bsplit;
         for (int s = 1; s < nsl; ++s) {
@@ -1216,7 +1219,11 @@ int ddpm_step_backward(float* d_params,
                        const float* d_dlogits, int batch, float grad_scale, float lr, unsigned flags,
                        float* d_grads, void* d_workspace, void* stream) {
     DDPM_CHECK_ARG(batch > 0, "ddpm_step_backward: batch must be positive (got %d)", batch);
-    DDPM_CHECK_ARG((flags & ~DDPM_BWD_TF32) == 0, "ddpm_step_backward: unknown flags %#x", flags);
+    DDPM_CHECK_ARG((flags & ~(DDPM_BWD_TF32 | DDPM_BWD_PART_SMALL | DDPM_BWD_PART_W1)) == 0, "ddpm_step_backward: unknown flags %#x", flags);
+    const bool part_small = (flags & DDPM_BWD_PART_SMALL) != 0, part_w1 = (flags & DDPM_BWD_PART_W1) != 0;
+    DDPM_CHECK_ARG(!(part_small && part_w1), "ddpm_step_backward: DDPM_BWD_PART_SMALL and DDPM_BWD_PART_W1 are two separate calls");
+    DDPM_CHECK_ARG(!(part_small || part_w1) || (d_dlogits == nullptr && grads_bsplit(batch) > 1),
+                   "ddpm_step_backward: the two-part backward is for batches >= 1024 of the fused-loss path");
     DDPM_CHECK_ARG(d_params && d_workspace, "ddpm_step_backward: null params/workspace");
     DDPM_CHECK_ARG(d_grads != nullptr || lr != 0.f, "ddpm_step_backward: nothing to do (no d_grads and lr == 0)");
     DDPM_CHECK_ARG(d_x != nullptr || (d_images != nullptr && d_idx != nullptr && n_samples > 0),
@@ -1245,7 +1252,9 @@ int ddpm_step_backward(float* d_params,
     g.B = batch; g.scale = grad_scale; g.lr = lr;
     g.bsplit = grads_bsplit(batch); g.gpart = (float*)(ws + L.gpart);
     g.bsplit_w1 = g.bsplit; g.skip_w1 = 0;
-    if ((flags & DDPM_BWD_TF32) && d_x == nullptr && batch >= 2048) {
+    g.skip_small = part_w1 ? 1 : 0;
+    if (part_small) g.skip_w1 = 2;                       // 2: skipped AND outside the range this call finalises
+    else if ((flags & DDPM_BWD_TF32) && d_x == nullptr && batch >= 2048) {
         // fc1's weight gradient (85 % of the flops of the backward pass) on the tensor cores.  Below 2048 rows the
         // 7 x slices grid leaves most SMs idle and the FFMA tiles are faster (measured: 46 vs 37 us at 1024).
         g.bsplit_w1 = dw1_tc_slices(batch); g.skip_w1 = 1;
@@ -1253,9 +1262,11 @@ int ddpm_step_backward(float* d_params,
                        "ddpm_step_backward: batch %d needs %d gradient slices, the workspace layout holds fewer", batch, g.bsplit_w1);
         if (launch_dw1_tc(g.dz1, d_images, n_samples, d_idx, batch, g.gpart, st)) return 1;
     }
-    if (d_x == nullptr) grads_kernel<true><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
-    else                grads_kernel<false><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
-    DDPM_CUDA(cudaGetLastError());
+    if (!(g.skip_small && g.skip_w1)) {                  // (dW1 alone from the tensor-core kernel: nothing left for this one)
+        if (d_x == nullptr) grads_kernel<true><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
+        else                grads_kernel<false><<<GRAD_ITEMS * g.bsplit, 256, 0, st>>>(g);
+        DDPM_CUDA(cudaGetLastError());
+    }
     if (g.bsplit > 1) {
         grads_finalize_kernel<<<116, 256, 0, st>>>(g);
         DDPM_CUDA(cudaGetLastError());

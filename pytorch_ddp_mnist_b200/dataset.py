@@ -57,6 +57,17 @@ class CDF5File:
             pass
 
 
+_PINNED = {}
+
+
+def _pinned_pair(slot: int, rows: int):
+    """Two page-locked staging buffers per reader thread, kept for the life of the process (cudaHostAlloc is slow)."""
+    key = (slot, rows)
+    if key not in _PINNED:
+        _PINNED[key] = [torch.empty((rows, IMG_BYTES), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    return _PINNED[key]
+
+
 class ResidentDataset:
     """u8 images [N,784] and labels [N] resident on one GPU."""
 
@@ -103,19 +114,44 @@ class ResidentDataset:
             images = torch.empty((per * world_size if gather else n, IMG_BYTES), dtype=torch.uint8, device=dev)
             labels = torch.empty((per * world_size if gather else n,), dtype=torch.uint8, device=dev)
             base = rank * per if gather else 0
-            # two pinned staging buffers: pread into one while the other is in flight to the GPU
-            stage = [torch.empty((chunk_rows, IMG_BYTES), dtype=torch.uint8).pin_memory() for _ in range(2)]
-            done = [torch.cuda.Event() for _ in range(2)]
+            # `nthreads` reader threads (DDPM_LOADER_THREADS; default 8, fewer on small hosts), each with two pinned staging buffers and its
+            # own copy stream: pread (positioned, thread-safe; the C call drops the GIL) into one buffer while the other
+            # is in flight to the GPU.  Measured on the 6 M-sample file (4.7 GB, page cache warm): 1 thread 5.9 GB/s,
+            # 4 threads 22.9 GB/s, 8 threads 34 GB/s into HBM (profiles/r02_scaled6m_*.json).
+            import threading
+            nthreads = max(1, int(os.environ.get("DDPM_LOADER_THREADS",
+                                                 str(min(8, max(2, (os.cpu_count() or 8) // max(world_size, 1)))))))
+            chunk_rows = min(chunk_rows, 1 << 14)
+            starts = list(range(r0, r1, chunk_rows))
+            errors = []
+
+            def reader(tix: int) -> None:
+                try:
+                    torch.cuda.set_device(dev)
+                    st = torch.cuda.Stream(device=dev)
+                    bufs = _pinned_pair(tix, chunk_rows)
+                    evs = [torch.cuda.Event(), torch.cuda.Event()]
+                    for i, s0 in enumerate(starts[tix::nthreads]):
+                        m = min(chunk_rows, r1 - s0)
+                        b = i & 1
+                        if i >= 2:
+                            evs[b].synchronize()
+                        f.read_rows("images", s0, m, bufs[b])
+                        with torch.cuda.stream(st):
+                            images[base + s0 - r0: base + s0 - r0 + m].copy_(bufs[b][:m], non_blocking=True)
+                            evs[b].record(st)
+                    st.synchronize()
+                except BaseException as e:               # surfaced by the caller
+                    errors.append(e)
+
+            threads = [threading.Thread(target=reader, args=(t,)) for t in range(min(nthreads, max(len(starts), 1)))]
+            for t in threads:
+                t.start()
+            for t in threads:
+                t.join()
+            if errors:
+                raise errors[0]
             copy_stream = torch.cuda.Stream(device=dev)
-            for i, s in enumerate(range(r0, r1, chunk_rows)):
-                m = min(chunk_rows, r1 - s)
-                b = i & 1
-                if i >= 2:
-                    done[b].synchronize()
-                f.read_rows("images", s, m, stage[b])
-                with torch.cuda.stream(copy_stream):
-                    images[base + s - r0: base + s - r0 + m].copy_(stage[b][:m], non_blocking=True)
-                    done[b].record(copy_stream)
             lab = torch.empty(max(r1 - r0, 1), dtype=torch.uint8).pin_memory()
             f.read_rows("labels", r0, r1 - r0, lab)
             with torch.cuda.stream(copy_stream):

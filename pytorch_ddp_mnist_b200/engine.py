@@ -56,6 +56,11 @@ class TrainEngine:
         self.ws = ops.Workspace(self.max_batch, self.device)
         self.step_count = 0                       # Philox stream position (perf-mode dropout)
         self.comm = None                          # fused data-parallel communicator (enable_fused_ddp)
+        import os as _os
+        # two-piece bucket at batch >= 1024, ws > 1 (the small piece's all-reduce overlaps fc1's weight-gradient kernel).
+        # Off by default: measured at batch 4096 it LOSES - 2 GPUs 121.6 vs 113.5 us/step, 8 GPUs 146.6 vs 129.4 - two
+        # NCCL launches and one more kernel cost more than the 71 KB all-reduce they hide (profiles/r02_b4096_*.json)
+        self.overlap_allreduce = _os.environ.get("DDPM_OVERLAP_ALLREDUCE") is not None
         self._feeds = {}                          # (batch, slots) -> ops.HostFeed (train_steps_host)
 
     # ------------------------------------------------------------------ parameters
@@ -132,9 +137,22 @@ class TrainEngine:
             ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, lr=self.lr, tf32=self.tf32)
         else:
             import torch.distributed as dist
-            ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
-                              grad_scale=1.0 / self.world_size, tf32=self.tf32)
-            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
+            if b >= 1024 and self.overlap_allreduce:
+                # the bucket leaves in two pieces, as DDP's hooks let it leave during backward (mp:439, 462): everything
+                # behind fc1's weights (71,680 B) is all-reduced while fc1's weight gradient is still being computed
+                small, big = self.grads[OFF_B1:], self.grads[:OFF_B1]
+                ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
+                                  grad_scale=1.0 / self.world_size, tf32=self.tf32, part="small")
+                w_small = dist.all_reduce(small, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
+                                  grad_scale=1.0 / self.world_size, tf32=self.tf32, part="w1")
+                w_big = dist.all_reduce(big, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                w_small.wait()
+                w_big.wait()
+            else:
+                ops.step_backward(self.params, self.ws, b, images=resident.images, idx=idx, grads=self.grads,
+                                  grad_scale=1.0 / self.world_size, tf32=self.tf32)
+                dist.all_reduce(self.grads, op=dist.ReduceOp.SUM, group=self.group)
             ops.sgd_step(self.params, self.grads, self.lr)
 
     def train_steps(self, resident, idx_flat: torch.Tensor, batch: int, nsteps: int,

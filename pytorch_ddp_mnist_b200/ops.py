@@ -132,7 +132,7 @@ def step_backward(params: torch.Tensor, ws: Workspace, batch: int, *,
                   images: Optional[torch.Tensor] = None, idx: Optional[torch.Tensor] = None,
                   x: Optional[torch.Tensor] = None, dlogits: Optional[torch.Tensor] = None,
                   grads: Optional[torch.Tensor] = None, grad_scale: float = 1.0, lr: float = 0.0,
-                  tf32: bool = False) -> None:
+                  tf32: bool = False, part: Optional[str] = None) -> None:
     _need(params, "params", torch.float32, (N_PARAMS,))
     _need(grads, "grads", torch.float32, (N_PARAMS,), optional=True)
     _need(dlogits, "dlogits", torch.float32, (batch, CLASSES), optional=True)
@@ -144,7 +144,8 @@ def step_backward(params: torch.Tensor, ws: Workspace, batch: int, *,
         _need(idx, "idx", torch.int64)
         n = images.shape[0]
     check(lib.ddpm_step_backward(ptr(params), ptr(images), n, ptr(idx), ptr(x), ptr(dlogits), batch,
-                                 grad_scale, lr, _lib.BWD_TF32 if tf32 else 0, ptr(grads), ptr(ws.buf), cur_stream()))
+                                 grad_scale, lr, (_lib.BWD_TF32 if tf32 else 0) | {None: 0, "small": _lib.BWD_PART_SMALL, "w1": _lib.BWD_PART_W1}[part],
+                                 ptr(grads), ptr(ws.buf), cur_stream()))
 
 
 def train_steps_persistent(params: torch.Tensor, ws: Workspace, batch: int, nsteps: int, *,

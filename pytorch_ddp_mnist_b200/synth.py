@@ -29,15 +29,21 @@ def templates(seed: int) -> np.ndarray:
     return np.random.default_rng([seed, 2 ** 31]).integers(0, 256, (10, 28, 28), dtype=np.uint8)
 
 
+def synth_chunk(n: int, seed: int, c: int, tpl_half: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """Chunk `c` (samples c*CHUNK ...) of ``synth(n, seed)``: chunks have independent generators, so they can be
+    produced in any order and by several processes."""
+    m = min(CHUNK, n - c * CHUNK)
+    rng = np.random.default_rng([seed, c])
+    labels = rng.integers(0, 10, m, dtype=np.uint8)
+    noise = rng.integers(0, 129, (m, 28, 28), dtype=np.uint8)
+    return tpl_half[labels] + noise, labels
+
+
 def synth_chunks(n: int, seed: int, template_seed: int = TEMPLATE_SEED
                  ) -> Iterator[Tuple[np.ndarray, np.ndarray]]:
     tpl = templates(template_seed) >> 1
-    for c, start in enumerate(range(0, n, CHUNK)):
-        m = min(CHUNK, n - start)
-        rng = np.random.default_rng([seed, c])
-        labels = rng.integers(0, 10, m, dtype=np.uint8)
-        noise = rng.integers(0, 129, (m, 28, 28), dtype=np.uint8)
-        yield tpl[labels] + noise, labels
+    for c in range(-(-n // CHUNK)):
+        yield synth_chunk(n, seed, c, tpl)
 
 
 def synth(n: int, seed: int) -> Tuple[np.ndarray, np.ndarray]:
@@ -50,6 +56,30 @@ def synth(n: int, seed: int) -> Tuple[np.ndarray, np.ndarray]:
         labs[pos:pos + len(lb)] = lb
         pos += len(lb)
     return imgs, labs
+
+
+def write_synth_file_part(path: str, n: int, seed: int, part: int, nparts: int, create: bool) -> None:
+    """One of `nparts` cooperating writers of the same file as write_synth_file (chunks part, part+nparts, ...).
+    The writer with `create=True` must run first (it writes the header and sizes the file); the others then fill
+    their chunks in place.  The result is byte-identical to write_synth_file's."""
+    dims = [("Y", 28), ("X", 28), ("idx", n)]
+    hdr, layout = cdf5.encode_header(
+        dims, [("images", cdf5.NC_UBYTE, (2, 0, 1)), ("labels", cdf5.NC_UBYTE, (2,))])
+    if create:
+        if os.path.exists(path):
+            os.remove(path)
+        with open(path, "wb") as f:
+            f.write(hdr)
+            f.truncate(layout["labels"].begin + layout["labels"].vsize)
+        return
+    tpl = templates(TEMPLATE_SEED) >> 1
+    with open(path, "r+b") as f:
+        for c in range(part, -(-n // CHUNK), nparts):
+            im, lb = synth_chunk(n, seed, c, tpl)
+            f.seek(layout["images"].begin + c * CHUNK * 784)
+            f.write(im.tobytes())
+            f.seek(layout["labels"].begin + c * CHUNK)
+            f.write(lb.tobytes())
 
 
 def write_synth_file(path: str, n: int, seed: int) -> None:

@@ -162,6 +162,30 @@ def main():
         ddp_err = check_ddp_wrapped_model(rank, world, local, dev, g)
     check_slab_loader(rank, world, dev)
 
+    # ---- large batch (BASELINE.json configs[3]): the bucket leaves in two pieces, the small one all-reduced while fc1's
+    #      weight gradient is still being computed; the result must equal the single all-reduce after backward
+    big_b = 1024
+    brng = np.random.default_rng(99)
+    bidx = torch.from_numpy(brng.integers(0, 60000, (world, 3, big_b)).astype(np.int64)[rank]).to(dev)
+    finals = []
+    for overlap in (True, False):
+        e = E.TrainEngine(dev, big_b, world_size=world, rank=rank)
+        e.overlap_allreduce = overlap
+        torch.manual_seed(3)
+        e.load_state_dict(E.init_params_like_reference())
+        e.broadcast_params(0)
+        for t in range(3):
+            e.train_step(res, bidx[t], philox_step=t)
+        torch.cuda.synchronize()
+        finals.append(e.params.clone())
+        other = e.params.clone()
+        dist.broadcast(other, src=0)
+        assert torch.equal(e.params, other), "large-batch replicas diverged"
+    # (NCCL may pick another algorithm, hence another summation order, for the smaller messages: tolerance, not bits)
+    rel = float((finals[0] - finals[1]).abs().max() / finals[1].abs().max())
+    assert rel < 1e-5, ("overlapped two-piece all-reduce differs from the single all-reduce", rel)
+    dist.barrier()
+
     # ---- BASELINE.json's ConvNet (not in the reference; oracle = restatement): bucket all-reduce over NCCL.
     # Each rank's gradient of its own 16-sample batch, pre-divided by ws and summed, must equal the gradient of the
     # mean loss over the global batch (the restatement evaluated on all ws x 16 samples), and replicas must agree.

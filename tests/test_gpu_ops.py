@@ -479,6 +479,31 @@ def test_tf32_tensor_core_fc1_matches_fp32_path(ops, dev, data, golden, batch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("batch,tf32", [(1024, False), (4096, False), (4096, True)])
+def test_two_part_backward_equals_one_call(ops, dev, data, golden, batch, tf32):
+    """DDPM_BWD_PART_SMALL then DDPM_BWD_PART_W1 (the data-parallel overlap of the bucket all-reduce with backward)
+    write bit for bit the bucket one plain call writes."""
+    g = golden["traj_ws1"]
+    images, labels, im, lb = data
+    rng = np.random.default_rng(batch + 5)
+    idx = torch.from_numpy(rng.integers(0, 60000, batch).astype(np.int64)).to(dev)
+    mask = torch.from_numpy((rng.random((batch, 128)) < 0.8).astype(np.uint8)).to(dev)
+    params = _flat(_params(g, "paramsN"), dev)
+    ws = ops.Workspace(batch, dev)
+    loss = torch.zeros(2, device=dev)
+    ops.step_forward(params, ws, batch, images=images, labels=labels, idx=idx, mask=mask, prep_backward=True, loss=loss, tf32=tf32)
+    one = torch.zeros(O.N_PARAMS, device=dev)
+    ops.step_backward(params, ws, batch, images=images, idx=idx, grads=one, grad_scale=0.25, tf32=tf32)
+    two = torch.full((O.N_PARAMS,), float("nan"), device=dev)
+    ops.step_backward(params, ws, batch, images=images, idx=idx, grads=two, grad_scale=0.25, tf32=tf32, part="small")
+    torch.cuda.synchronize()
+    assert bool(torch.isnan(two[:100352]).all()) and bool(torch.isfinite(two[100352:]).all())   # only its own range
+    ops.step_backward(params, ws, batch, images=images, idx=idx, grads=two, grad_scale=0.25, tf32=tf32, part="w1")
+    torch.cuda.synchronize()
+    assert torch.equal(one, two)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("batch", [8192, 9000])
 def test_tf32_backward_stays_inside_workspace_beyond_batch_7168(ops, dev, data, golden, batch):
     """dw1_tc_kernel writes one gradient slice per 224 rows (37 at batch 8192) while grads_kernel's own slicing is
