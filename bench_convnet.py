@@ -91,13 +91,20 @@ def quick_record(torch, dev, B, world, rank, dist, steps=150, warmup=10):
     eng.broadcast_params()
     for t in range(warmup):
         eng.train_step(res, idx[t * B:(t + 1) * B])
+    chunk = 10                                                # CUDA graph of 10 unrolled steps, index buffer refilled per replay
+    steps = (steps // chunk) * chunk
+    buf = torch.empty(chunk * B, dtype=torch.int64, device=dev)
+    graph = eng.capture_steps(res, list(torch.split(buf, B)))
+    buf.copy_(idx[:chunk * B])
+    graph.replay()
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for t in range(warmup, warmup + steps):
-        eng.train_step(res, idx[t * B:(t + 1) * B])
+    for t in range(warmup, warmup + steps, chunk):
+        buf.copy_(idx[t * B:(t + chunk) * B])
+        graph.replay()
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
@@ -149,9 +156,23 @@ def run(args, clock_sampler_cls, peaks_fn, metric) -> None:
     eng.load_state_dict(cn.init_params_like_torch())
     eng.broadcast_params()
 
+    # the step is 13 (TF32) / 10 (fp32) dependent launches: replayed as a CUDA graph of `chunk` unrolled steps whose
+    # index buffer is refilled before every replay (`--no-graph`-style eager launches remain for the tail)
+    chunk = 10
+    gbuf = torch.empty(chunk * B, dtype=torch.int64, device=dev)
+    for t in range(2):
+        eng.train_step(res, shard_dev[t * B:(t + 1) * B])
+    graph = eng.capture_steps(res, list(torch.split(gbuf, B)))
+
     def steps(n, start):
-        for t in range(start, start + n):
+        t = start
+        while t + chunk <= start + n:
+            gbuf.copy_(shard_dev[t * B:(t + chunk) * B])
+            graph.replay()
+            t += chunk
+        while t < start + n:
             eng.train_step(res, shard_dev[t * B:(t + 1) * B])
+            t += 1
 
     steps(W, 0)
     torch.cuda.synchronize()
@@ -284,7 +305,8 @@ def run(args, clock_sampler_cls, peaks_fn, metric) -> None:
                                    f"(SURVEY.md §0); oracle = restatement, parity unpinned",
                        "batch_per_rank": B, "dataset_samples": N, "final_batch_loss": final_loss,
                        "l2": "resident u8 dataset 188 MB (> 126 MB L2), fresh rows every step",
-                       "gradient_exchange": "NCCL all-reduce of the 4,799,528-byte bucket between backward and Adadelta (ws > 1)"},
+                       "gradient_exchange": "NCCL all-reduce of the 4,799,528-byte bucket between backward and Adadelta (ws > 1)",
+                       "step_launch": "CUDA graph of 10 unrolled steps, index buffer refilled per replay"},
             "gpu_launches": K * (13 if tf32 else 10), "clocks": clocks, "e2e": e2e, "roofline": roof, "kernels": kernels}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
