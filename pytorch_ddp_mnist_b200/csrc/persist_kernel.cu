@@ -387,6 +387,61 @@ __device__ __forceinline__ void ll_stage(const unsigned long long* base, size_t 
     }
 }
 
+// Two tiles of the same rows at once (the dW2 / dW3 CTAs need an early and a late quantity of every row): the polls of
+// both are in flight together, so the wait ends one L2 round trip after the LATER one arrived instead of two.
+template <int NA, int NB>
+__device__ __forceinline__ void ll_stage_pair(const unsigned long long* base_a, float* dst_a, int ld_a,
+                                              const unsigned long long* base_b, float* dst_b, int ld_b,
+                                              size_t row_stride, int nrows, unsigned t32, int* err) {
+    constexpr int PA = NA / 2, PB = NB / 2, TA = CR * PA / P_THREADS, TB = CR * PB / P_THREADS;
+    static_assert(CR * PA % P_THREADS == 0 && CR * PB % P_THREADS == 0, "tiles must divide evenly");
+    unsigned xa0[TA], fa0[TA], xa1[TA], fa1[TA], xb0[TB], fb0[TB], xb1[TB], fb1[TB];
+    auto load_a = [&](int i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PA, c2 = (e - r * PA) * 2;
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(xa0[i]), "=r"(fa0[i]), "=r"(xa1[i]), "=r"(fa1[i])
+                     : "l"(base_a + (size_t)r * row_stride + c2) : "memory");
+    };
+    auto load_b = [&](int i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PB, c2 = (e - r * PB) * 2;
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(xb0[i]), "=r"(fb0[i]), "=r"(xb1[i]), "=r"(fb1[i])
+                     : "l"(base_b + (size_t)r * row_stride + c2) : "memory");
+    };
+#pragma unroll
+    for (int i = 0; i < TA; ++i) {
+        xa0[i] = xa1[i] = 0u; fa0[i] = fa1[i] = t32;
+        if ((threadIdx.x + i * P_THREADS) / PA < nrows) load_a(i);
+    }
+#pragma unroll
+    for (int i = 0; i < TB; ++i) {
+        xb0[i] = xb1[i] = 0u; fb0[i] = fb1[i] = t32;
+        if ((threadIdx.x + i * P_THREADS) / PB < nrows) load_b(i);
+    }
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    for (;;) {
+        bool missing = false;
+#pragma unroll
+        for (int i = 0; i < TA; ++i) missing |= (fa0[i] != t32 || fa1[i] != t32);
+#pragma unroll
+        for (int i = 0; i < TB; ++i) missing |= (fb0[i] != t32 || fb1[i] != t32);
+        if (!missing || poll_miss(err, t0, spins)) break;
+#pragma unroll
+        for (int i = 0; i < TA; ++i) if (fa0[i] != t32 || fa1[i] != t32) load_a(i);
+#pragma unroll
+        for (int i = 0; i < TB; ++i) if (fb0[i] != t32 || fb1[i] != t32) load_b(i);
+    }
+#pragma unroll
+    for (int i = 0; i < TA; ++i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PA, c2 = (e - r * PA) * 2;
+        *reinterpret_cast<float2*>(&dst_a[r * ld_a + c2]) = make_float2(__uint_as_float(xa0[i]), __uint_as_float(xa1[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < TB; ++i) {
+        const int e = threadIdx.x + i * P_THREADS, r = e / PB, c2 = (e - r * PB) * 2;
+        *reinterpret_cast<float2*>(&dst_b[r * ld_b + c2]) = make_float2(__uint_as_float(xb0[i]), __uint_as_float(xb1[i]));
+    }
+}
+
 // FEED: host-fed mode (batches arrive in a device ring while the kernel runs); DDP: world > 1 (in-kernel gradient
 // exchange) - a template parameter so that the single-GPU kernel carries none of the exchange code or its registers
 template <bool FEED, bool DDP>
@@ -461,13 +516,15 @@ train_persist_kernel(PersistArgs a) {
         float host_loss = 0.f;
         unsigned long long feed_probe = 0;
         // Row CTAs fetch this step's W2 (into registers: thread (jb, kb) keeps the 8x8 block W2[jb*8.., kb*8..], used by
-        // both the forward product, reduced over kb, and the backward product, reduced over jb) and W3 / b2 (into smem).
-        // They may do so once the 'ready' counter shows that the 36 owner CTAs finished last step's updates, which is
-        // about 1,000-1,700 cycles into this step.  EVERY thread samples the counter itself at the top of the step and
-        // looks at its sample at two points inside phase A: no broadcast, no barrier, and the 64 KB arrive while phase A
-        // computes (issued after phase A, they held the partial-sum polls up for ~3,000 cycles: 64 SMs pull the same
-        // lines).  (No fence: the owners released their updates before bumping the counter; the loads below are
-        // L2-coherent .cg / cp.async loads issued after the sample showed the count.)
+        // both the forward product, reduced over kb, and the backward product, reduced over jb) and W3 / b2 (into smem)
+        // once the 'ready' counter shows that the 36 owner CTAs finished last step's updates.  EVERY thread samples the
+        // counter itself (no broadcast, no barrier): at the top of the step, and again right after phase A, where the
+        // loads are issued.  (Tried, %globaltimer-stamped: looking at the sample INSIDE phase A and issuing the loads
+        // there - the 64 KB arrive earlier, but the loop around them takes 2,250 ns instead of 1,310 and the step time is
+        // the same; a TMA bulk copy into smem issued by one thread - same result.  The chain that binds is
+        // dz2 -> dW2 tiles -> release -> this fetch -> z2, profiles/r02_phase_timeline_1gpu_globaltimer.txt.)
+        // (No fence: the owners released their updates before bumping the counter; the loads are L2-coherent .cg /
+        // cp.async loads issued after the sample showed the count.)
         float blk[8][8];
         bool params_loaded = false;
         const unsigned long long ready_need = s.ready_base + (unsigned long long)N_READY * step;
@@ -479,9 +536,6 @@ train_persist_kernel(PersistArgs a) {
             if (tid < HID / 4) __pipeline_memcpy_async(&s.b2[tid * 4], a.params + DDPM_OFF_B2 + tid * 4, 16); \
             else if (tid < HID / 2 && step == 0) __pipeline_memcpy_async(&s.b1[(tid - HID / 4) * 4], a.params + DDPM_OFF_B1 + (tid - HID / 4) * 4, 16); \
             __pipeline_commit(); params_loaded = true; DBG_STAMP(13); } while (0)
-#define PARAM_LOADS_TRY() do { if (cta < B && !params_loaded) { \
-            if (step == 0 || ready_seen >= ready_need) PARAM_LOADS(); \
-            else ready_seen = ld_relaxed64(ready); } } while (0)
 
         // ================================ phase A ================================
         if (own_w1) {
@@ -505,10 +559,6 @@ train_persist_kernel(PersistArgs a) {
                 float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int n4 = 0; n4 < NT / 4; ++n4) {
-                    // looks at the counter: six, ~200 ns apart, on one GPU (the count is there within the first two); with
-                    // a cross-GPU exchange in front of it the count comes late and every look would wait for the previous
-                    // sample's round trip (+2,000 cycles of phase A, measured): two looks then
-                    if (single && (DDP ? (n4 == 5 || n4 == 11) : ((n4 & 1) && n4 < 13))) PARAM_LOADS_TRY();
                     const float4 w = *reinterpret_cast<const float4*>(&s.w1t[w1_idx(m, n4 * 4)]);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
@@ -854,8 +904,8 @@ train_persist_kernel(PersistArgs a) {
                 __syncthreads();
                 const int nrows = B - c * CR < CR ? B - c * CR : CR;
                 const unsigned long long* rows0 = my_act + (size_t)(c * CR) * LL_ACT_WORDS;
-                ll_stage<32>(rows0 + ACT_H1D + kt * 32, LL_ACT_WORDS, nrows, tl, hst, 32, a.lerr);     // produced first
-                ll_stage<MT>(rows0 + ACT_DZ2 + jt * 16, LL_ACT_WORDS, nrows, tl, s.dzt, MT, a.lerr);
+                ll_stage_pair<32, MT>(rows0 + ACT_H1D + kt * 32, hst, 32, rows0 + ACT_DZ2 + jt * 16, s.dzt, MT,
+                                      LL_ACT_WORDS, nrows, tl, a.lerr);
                 __syncthreads();
                 if (c == 0) DBG_STAMP(4);
 #pragma unroll
@@ -917,8 +967,8 @@ train_persist_kernel(PersistArgs a) {
                 __syncthreads();
                 const int nrows = B - c * CR < CR ? B - c * CR : CR;
                 const unsigned long long* rows0 = my_act + (size_t)(c * CR) * LL_ACT_WORDS;
-                ll_stage<32>(rows0 + ACT_H2 + kt * 32, LL_ACT_WORDS, nrows, tl, hst, 32, a.lerr);
-                ll_stage<NCP>(rows0 + ACT_DZ3, LL_ACT_WORDS, nrows, tl, s.dzt, MT, a.lerr);
+                ll_stage_pair<32, NCP>(rows0 + ACT_H2 + kt * 32, hst, 32, rows0 + ACT_DZ3, s.dzt, MT,
+                                       LL_ACT_WORDS, nrows, tl, a.lerr);
                 __syncthreads();
                 if (c == 0) DBG_STAMP(4);
 #pragma unroll
@@ -934,18 +984,8 @@ train_persist_kernel(PersistArgs a) {
                     acc[9] = fmaf(d2.y, hv, acc[9]);
                 }
             }
-            float lsum = 0.f;
-            if (kt == 2) {                                       // per-row losses (stored before that row's dz3)
-                const long long t0 = clock64();
-                for (int row = tid; row < B; row += P_THREADS) {
-                    float lv[1];
-                    ll_poll<1>(a.lerr, my_loss + row, tl, t0, lv);
-                    lsum += lv[0];
-                }
-            }
 #pragma unroll
             for (int i = 0; i < NC; ++i) pb[(bq * NC + i) * 32 + k] = acc[i];
-            if (kt == 2) s.red[tid] = lsum;
             __syncthreads();
             {
                 float g0 = 0.f, g1 = 0.f;
@@ -966,6 +1006,21 @@ train_persist_kernel(PersistArgs a) {
                 grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
             }
+            if (a.lr != 0.f) {                                   // W3 of the next step is in place: publish it BEFORE the loss
+                __syncthreads();                                 // bookkeeping below (the rows of the next step wait for
+                if (tid == 0) red_release64(ready);              // the slowest of the 36 publishers, and this was it)
+            }
+            if (kt == 2) {                                       // per-row losses (stored before that row's dz3)
+                float lsum = 0.f;
+                const long long t0 = clock64();
+                for (int row = tid; row < B; row += P_THREADS) {
+                    float lv[1];
+                    ll_poll<1>(a.lerr, my_loss + row, tl, t0, lv);
+                    lsum += lv[0];
+                }
+                s.red[tid] = lsum;
+                __syncthreads();
+            }
             if (kt == 2 && warp == 0) {
                 // batch loss: 256 strided partial sums -> 32 lanes (fixed order) -> shuffle tree
                 float v = 0.f;
@@ -983,7 +1038,7 @@ train_persist_kernel(PersistArgs a) {
                 }
             }
         }
-        if (!own_w1 && a.lr != 0.f) {                         // W2 / W3 / b2 of the next step are in place
+        if (!own_w1 && cta < CTA_W3 && a.lr != 0.f) {         // W2 / b2 of the next step are in place
             __syncthreads();
             if (tid == 0) red_release64(ready);
         }
