@@ -83,6 +83,12 @@ int    ddpm_workspace_init(void* d_workspace, int max_batch, void* stream);
  * rest of ddpm_workspace_bytes() holds the persistent kernel's tagged dataflow words.  ddpm_step_forward_static_scratch's
  * built-in array is this many bytes for its row limit. */
 size_t ddpm_workspace_forward_bytes(int max_batch);
+/* Test aid (no counterpart in the reference): copies one of the per-layer arrays that ddpm_step_forward(PREP_BACKWARD)
+ * / ddpm_step_backward left in the workspace to d_out - which = 0 h1d (dropout(relu(fc1)), mp:415-417), 1 h2
+ * (relu(fc2), mp:418-419), 2 dz2, 3 dz1 (f32 [batch][128]), 4 dlogits (f32 [batch][16], 10 used; the logits
+ * themselves leave through ddpm_step_forward's d_logits).  The parity
+ * tests compare them with the reference's own per-layer activations (tests/golden/traj_ws1.npz acts0.*). */
+int ddpm_workspace_peek(const void* d_workspace, int batch, int which, float* d_out, void* stream);
 
 #define DDPM_FWD_PREP_BACKWARD 1u  /* also compute dL/dz2, dL/dz1 from the CE gradient (training) */
 #define DDPM_FWD_PHILOX_MASK   2u  /* draw the dropout mask in-kernel (seed, step); d_mask unused */

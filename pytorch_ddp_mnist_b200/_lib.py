@@ -51,6 +51,7 @@ SIGNATURES = {
     "ddpm_workspace_bytes": (C.c_size_t, [_i32]),
     "ddpm_workspace_init": (_i32, [_vp, _i32, _vp]),
     "ddpm_workspace_forward_bytes": (C.c_size_t, [_i32]),
+    "ddpm_workspace_peek": (_i32, [_vp, _i32, _i32, _vp, _vp]),
     "ddpm_step_forward": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _u64, _u64, _i32, _u32,
                                  _vp, _vp, _vp, _vp]),
     "ddpm_step_forward_static_scratch": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _u64, _u64, _i32,

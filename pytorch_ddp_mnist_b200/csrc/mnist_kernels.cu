@@ -1152,6 +1152,16 @@ size_t ddpm_workspace_bytes(int max_batch) {
     return ws_layout(max_batch).total;
 }
 
+int ddpm_workspace_peek(const void* d_workspace, int batch, int which, float* d_out, void* stream) {
+    DDPM_CHECK_ARG(d_workspace && d_out && batch > 0, "ddpm_workspace_peek: bad arguments");
+    const WsLayout L = ws_layout(batch);
+    const size_t off[5] = {L.h1d, L.h2, L.dz2, L.dz1, L.dz3};
+    DDPM_CHECK_ARG(which >= 0 && which < 5, "ddpm_workspace_peek: which must be 0..4 (h1d, h2, dz2, dz1, dz3)");
+    const size_t n = (size_t)batch * (which < 4 ? HID : NCP) * sizeof(float);
+    DDPM_CUDA(cudaMemcpyAsync(d_out, (const char*)d_workspace + off[which], n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}
+
 size_t ddpm_workspace_forward_bytes(int max_batch) {
     if (max_batch <= 0) return 0;
     return ws_layout(max_batch).fend;

@@ -88,6 +88,15 @@ class Workspace:
     def nbytes(self) -> int:
         return self.buf.numel()
 
+    def peek(self, batch: int, which: str) -> torch.Tensor:
+        """Test aid: one of the per-layer arrays the three-kernel forward / backward left in the workspace
+        (`h1d`, `h2`, `dz2`, `dz1`: [batch,128]; `dz3`: [batch,16])."""
+        names = ("h1d", "h2", "dz2", "dz1", "dz3")
+        w = names.index(which)
+        out = torch.empty((batch, 128 if w < 4 else 16), dtype=torch.float32, device=self.buf.device)
+        check(lib.ddpm_workspace_peek(ptr(self.buf), batch, w, ptr(out), cur_stream()))
+        return out
+
     def error(self) -> int:
         """Non-zero once a wait inside the persistent kernel gave up (~3 s): see ddpm_workspace_error.  Blocking."""
         import ctypes as C
