@@ -1337,6 +1337,9 @@ extern "C" int ddpm_train_steps_fused_ddp(
     //  multiplies ws x 64 rows of pixels per tile, which outweighs the saved traffic beyond 4 ranks; DDPM_ACT_EXCHANGE=1 forces it)
     const bool act_default = comm->world <= 4 || getenv("DDPM_ACT_EXCHANGE") != nullptr;
     a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && act_default && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
+    // with the dz1 exchange only 71 KB of the bucket are left to exchange: everyone pushes them to everyone (one NVLink
+    // hop, (ws-1) x 142 KB out per GPU) instead of the two-stage push-sum-push that the full 946 KB need beyond 2 ranks
+    if (a.act_exchange && getenv("DDPM_EXCHANGE") == nullptr) a.two_stage = 0;
     a.idx_all = d_idx_all; a.idx_stride = (size_t)idx_stride;
     if (d_idx == nullptr && d_idx_all != nullptr) d_idx = d_idx_all + (size_t)comm->rank * idx_stride;
     const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,
