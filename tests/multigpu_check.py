@@ -213,6 +213,30 @@ def main():
     dist.broadcast(other, src=0)
     assert torch.equal(mine, other), "convnet replicas diverged"
     dist.barrier()
+    # ---- a peer that never shows up: the waiting kernel gives up after ~3 s, every later wait within microseconds
+    #      (the error word is sticky), and the host sees the error - no rank holds its GPU for minutes
+    import time
+    lone = E.TrainEngine(dev, 64, world_size=world, rank=rank)
+    torch.manual_seed(5)
+    lone.load_state_dict(E.init_params_like_reference())
+    lone.enable_fused_ddp()
+    dist.barrier()
+    if rank == 0:
+        lidx = torch.from_numpy(O.shard_indices(60000, world, 0)[:40 * 64]).to(dev)
+        t0 = time.perf_counter()
+        lone.train_steps(res, lidx, 64, 40)                   # 40 steps, nobody else joins
+        torch.cuda.synchronize()
+        waited = time.perf_counter() - t0
+        assert lone.comm.error() != 0, "the exchange time-out did not raise the communicator's error word"
+        assert waited < 12.0, f"a missing peer held the kernel for {waited:.1f} s (the bound is ~3 s, sticky afterwards)"
+        try:
+            lone.check_comm()
+            raise AssertionError("check_comm() did not raise")
+        except RuntimeError:
+            pass
+    dist.barrier()
+    del lone
+
     if rank == 0:
         import json
         print("PARITY_GATE " + json.dumps(rec))
