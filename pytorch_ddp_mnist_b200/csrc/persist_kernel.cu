@@ -72,6 +72,7 @@ struct PersistArgs {
     long long* dbg;                                   // optional [grid][8 steps][16] clock64 stamps (profiling aid)
     // ---- fused data-parallel mode (world > 1): gradient tiles are exchanged over NVLink peer memory
     int world, rank, two_stage;
+    int two_stage_small;                              // ... for the 71 KB behind fc1's weights (b1, W2, b2, W3)
     unsigned long long comm_step;                     // number of fused steps this communicator ran before this launch
     unsigned long long* xrecv[DDPM_MAX_WORLD];        // every rank's receive buffer [2 parities][world sources][NP] of
                                                       // 8-byte (value, step) words, peer-mapped
@@ -286,23 +287,25 @@ __device__ __forceinline__ void ll_poll(int* err, const unsigned long long* src,
 // one L2 round trip after the last source arrived, not one per source.
 // Split in two so that a thread with several exchanges (a tile and a bias, two classes of W3) has all of them on the
 // wire before it waits for any: ll_ar_begin = this thread's first-hop pushes, ll_ar_end = everything else.
-template <int N>
+template <int N, bool SMALL = false>
 __device__ __forceinline__ void ll_ar_begin(const PersistArgs& a, unsigned long long T, int home, int off, const float (&v)[N]) {
     const unsigned t32 = (unsigned)T;
     const size_t par = (size_t)(T & 1) * a.world;
-    if (a.two_stage) {
+    const int two_stage = SMALL ? a.two_stage_small : a.two_stage;
+    if (two_stage) {
         if (home != a.rank) ll_store<N>(a.xrecv[home] + (par + a.rank) * NP + off, t32, v);
     } else {
         for (int r = 0; r < a.world; ++r)
             if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, v);
     }
 }
-template <int N>
+template <int N, bool SMALL = false>
 __device__ __forceinline__ void ll_ar_end(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
     const unsigned t32 = (unsigned)T;
     const size_t par = (size_t)(T & 1) * a.world;
     const long long t0 = clock64();
-    const bool is_home = !a.two_stage || home == a.rank;
+    const int two_stage = SMALL ? a.two_stage_small : a.two_stage;
+    const bool is_home = !two_stage || home == a.rank;
     if (!is_home) {
         ll_poll<N>(a.xerr, a.xrecv[a.rank] + (par + home) * NP + off, t32, t0, v);
         return;
@@ -335,17 +338,17 @@ __device__ __forceinline__ void ll_ar_end(const PersistArgs& a, unsigned long lo
 #pragma unroll
             for (int i = 0; i < N; ++i) sum[i] += __uint_as_float(x[r][i]);
         }
-    if (a.two_stage) {
+    if (two_stage) {
         for (int r = 0; r < a.world; ++r)
             if (r != a.rank) ll_store<N>(a.xrecv[r] + (par + a.rank) * NP + off, t32, sum);
     }
 #pragma unroll
     for (int i = 0; i < N; ++i) v[i] = sum[i];
 }
-template <int N>
+template <int N, bool SMALL = false>
 __device__ __forceinline__ void ll_allreduce(const PersistArgs& a, unsigned long long T, int home, int off, float (&v)[N]) {
-    ll_ar_begin<N>(a, T, home, off, v);
-    ll_ar_end<N>(a, T, home, off, v);
+    ll_ar_begin<N, SMALL>(a, T, home, off, v);
+    ll_ar_end<N, SMALL>(a, T, home, off, v);
 }
 
 // dst[r][0..NCOLS) for rows r < CR from tagged words at base[r * row_stride + c] (polled until they carry tag
@@ -880,7 +883,7 @@ train_persist_kernel(PersistArgs a) {
                 }
             } else if (b1_thread) {                              // alongside the tile update above
                 float gb[1] = {db_acc * a.gscale};
-                if (ddp && !actx) ll_allreduce<1>(a, T, (tid - W1_ACTIVE) % a.world, offb1, gb);
+                if (ddp && !actx) ll_allreduce<1, true>(a, T, (tid - W1_ACTIVE) % a.world, offb1, gb);
                 grad_out(a.grads, a.lr, a.params, offb1, gb[0], pold_b1);
                 if (a.lr != 0.f)
                     ll_store1(a.llb1 + (size_t)((TL + 1) & 1) * HID + mt * MT + (tid - W1_ACTIVE), (unsigned)(TL + 1),
@@ -941,10 +944,10 @@ train_persist_kernel(PersistArgs a) {
                 const int offb = DDPM_OFF_B2 + jt * 16 + tid;
                 float gb[1] = {db_acc * a.gscale};
                 if (ddp) {                                       // tile and bias on the wire before either wait
-                    ll_ar_begin<2>(a, T, home_sm, off, g);
-                    if (do_db) ll_ar_begin<1>(a, T, tid % a.world, offb, gb);
-                    ll_ar_end<2>(a, T, home_sm, off, g);
-                    if (do_db) ll_ar_end<1>(a, T, tid % a.world, offb, gb);
+                    ll_ar_begin<2, true>(a, T, home_sm, off, g);
+                    if (do_db) ll_ar_begin<1, true>(a, T, tid % a.world, offb, gb);
+                    ll_ar_end<2, true>(a, T, home_sm, off, g);
+                    if (do_db) ll_ar_end<1, true>(a, T, tid % a.world, offb, gb);
                 }
                 grad_out(a.grads, a.lr, a.params, off, g[0], pold.x);
                 grad_out(a.grads, a.lr, a.params, off + 1, g[1], pold.y);
@@ -998,10 +1001,10 @@ train_persist_kernel(PersistArgs a) {
                 }
                 float ga[1] = {g0 * a.gscale}, gc[1] = {g1 * a.gscale};
                 if (ddp) {                                       // both classes on the wire before either wait
-                    ll_ar_begin<1>(a, T, home_sm, o0, ga);
-                    if (c1 < NC) ll_ar_begin<1>(a, T, home_sm, o1, gc);
-                    ll_ar_end<1>(a, T, home_sm, o0, ga);
-                    if (c1 < NC) ll_ar_end<1>(a, T, home_sm, o1, gc);
+                    ll_ar_begin<1, true>(a, T, home_sm, o0, ga);
+                    if (c1 < NC) ll_ar_begin<1, true>(a, T, home_sm, o1, gc);
+                    ll_ar_end<1, true>(a, T, home_sm, o0, ga);
+                    if (c1 < NC) ll_ar_end<1, true>(a, T, home_sm, o1, gc);
                 }
                 grad_out(a.grads, a.lr, a.params, o0, ga[0], p0);
                 if (c1 < NC) grad_out(a.grads, a.lr, a.params, o1, gc[0], p1);
@@ -1087,7 +1090,7 @@ exchange_only_kernel(PersistArgs a) {
             } else if (nt == 0 && tid < W1_ACTIVE + MT) {
                 const int offb = DDPM_OFF_B1 + mt * MT + (tid - W1_ACTIVE);
                 float gb[1] = {contrib(offb, step)};
-                ll_allreduce<1>(a, T, (tid - W1_ACTIVE) % a.world, offb, gb);
+                ll_allreduce<1, true>(a, T, (tid - W1_ACTIVE) % a.world, offb, gb);
                 if (last) a.xout[offb] = gb[0];
             }
         } else if (cta < CTA_W3) {
@@ -1097,20 +1100,20 @@ exchange_only_kernel(PersistArgs a) {
             const bool do_db = kt == 0 && tid < 16;
             const int offb = DDPM_OFF_B2 + jt * 16 + tid;
             float gb[1] = {contrib(offb, step)};
-            ll_ar_begin<2>(a, T, home_sm, off, g);
-            if (do_db) ll_ar_begin<1>(a, T, tid % a.world, offb, gb);
-            ll_ar_end<2>(a, T, home_sm, off, g);
-            if (do_db) ll_ar_end<1>(a, T, tid % a.world, offb, gb);
+            ll_ar_begin<2, true>(a, T, home_sm, off, g);
+            if (do_db) ll_ar_begin<1, true>(a, T, tid % a.world, offb, gb);
+            ll_ar_end<2, true>(a, T, home_sm, off, g);
+            if (do_db) ll_ar_end<1, true>(a, T, tid % a.world, offb, gb);
             if (last) { a.xout[off] = g[0]; a.xout[off + 1] = g[1]; }
             if (last && do_db) a.xout[offb] = gb[0];
         } else {
             const int kt = cta - CTA_W3, k = tid & 31, c0 = tid >> 5, c1 = c0 + 8;
             const int o0 = DDPM_OFF_W3 + c0 * HID + kt * 32 + k, o1 = DDPM_OFF_W3 + c1 * HID + kt * 32 + k;
             float ga[1] = {contrib(o0, step)}, gc[1] = {contrib(o1, step)};
-            ll_ar_begin<1>(a, T, home_sm, o0, ga);
-            if (c1 < NC) ll_ar_begin<1>(a, T, home_sm, o1, gc);
-            ll_ar_end<1>(a, T, home_sm, o0, ga);
-            if (c1 < NC) ll_ar_end<1>(a, T, home_sm, o1, gc);
+            ll_ar_begin<1, true>(a, T, home_sm, o0, ga);
+            if (c1 < NC) ll_ar_begin<1, true>(a, T, home_sm, o1, gc);
+            ll_ar_end<1, true>(a, T, home_sm, o0, ga);
+            if (c1 < NC) ll_ar_end<1, true>(a, T, home_sm, o1, gc);
             if (last) a.xout[o0] = ga[0];
             if (last && c1 < NC) a.xout[o1] = gc[0];
         }
@@ -1309,6 +1312,12 @@ extern "C" void ddpm_comm_destroy(ddpm_comm* c) {
 static void comm_fill(PersistArgs& a, const ddpm_comm* comm) {
     a.world = comm->world; a.rank = comm->rank; a.comm_step = comm->steps;
     a.two_stage = comm->two_stage;
+    // the 71 KB behind fc1's weights: one-shot (one NVLink hop instead of two in front of the W2 / W3 update that the
+    // next step's rows wait for) unless DDPM_SMALL_EXCHANGE=two_stage
+    {
+        const char* e = getenv("DDPM_SMALL_EXCHANGE");
+        a.two_stage_small = e ? (strcmp(e, "two_stage") == 0) : comm->two_stage;
+    }
     for (int r = 0; r < comm->world; ++r) {
         a.xrecv[r] = (unsigned long long*)comm->peer[r];
         a.xrecv_dz[r] = (unsigned long long*)((char*)comm->peer[r] + comm->recv_bytes);
@@ -1339,7 +1348,7 @@ extern "C" int ddpm_train_steps_fused_ddp(
     a.act_exchange = (d_idx_all != nullptr && batch <= CR && comm->world > 1 && act_default && getenv("DDPM_NO_ACT_EXCHANGE") == nullptr) ? 1 : 0;
     // with the dz1 exchange only 71 KB of the bucket are left to exchange: everyone pushes them to everyone (one NVLink
     // hop, (ws-1) x 142 KB out per GPU) instead of the two-stage push-sum-push that the full 946 KB need beyond 2 ranks
-    if (a.act_exchange && getenv("DDPM_EXCHANGE") == nullptr) a.two_stage = 0;
+    if (a.act_exchange && getenv("DDPM_EXCHANGE") == nullptr) a.two_stage = a.two_stage_small = 0;
     a.idx_all = d_idx_all; a.idx_stride = (size_t)idx_stride;
     if (d_idx == nullptr && d_idx_all != nullptr) d_idx = d_idx_all + (size_t)comm->rank * idx_stride;
     const int rc = persist_fill_and_launch(a, d_params, nullptr, d_images, d_labels, n_samples, d_idx, d_masks,
