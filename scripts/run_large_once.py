@@ -12,6 +12,6 @@ eng = E.TrainEngine(dev, B); eng.load_state_dict(E.init_params_like_reference())
 idx = torch.randperm(60000, device=dev).to(torch.int64)
 for i in range(4):
     ops.step_forward(eng.params, eng.ws, B, images=images, labels=labels, idx=idx[i * B:(i + 1) * B], philox=(1, i), prep_backward=True, loss=eng.loss, tf32=True)
-    ops.step_backward(eng.params, eng.ws, B, images=images, idx=idx[i * B:(i + 1) * B], lr=0.01)
+    ops.step_backward(eng.params, eng.ws, B, images=images, idx=idx[i * B:(i + 1) * B], lr=0.01, tf32=True)
 torch.cuda.synchronize()
 print("loss", float(eng.loss[0]))
