@@ -589,16 +589,6 @@ train_persist_kernel(PersistArgs a) {
         if (cta < B) {
             const int j = tid & 127, h = tid >> 7;
             const int jb = tid >> 4, kb = tid & 15;
-            if (!params_loaded) {                             // not seen during phase A (or no phase A in this CTA): wait
-                const long long t0 = clock64();
-                unsigned spins = 0;
-                while (step > 0 && ready_seen < ready_need) {
-                    if (poll_miss(a.lerr, t0, spins)) break;
-                    ready_seen = ld_relaxed64(ready);
-                }
-                PARAM_LOADS();
-            }
-            DBG_STAMP(14);
             float* red2 = s.w2;                               // [16][RLD] partial products (padded: conflict-free float4 stores)
             constexpr int RLD = HID + 4;
             bool staged = false;
@@ -623,6 +613,13 @@ train_persist_kernel(PersistArgs a) {
                     const unsigned long long* pb = a.llb1 + parl * HID + j;
                     unsigned bx = 0, bf = tl;
                     if (poll_b1) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(bx), "=r"(bf) : "l"(pb) : "memory");
+                    // the launch's first step takes b1 from the parameters too (no tagged word yet), and nothing has to be
+                    // waited for: request W2 / W3 / b2 / b1 right away.  Later steps: a fresh sample of the 'ready' counter
+                    // travels with the polls (the one from the top of the step is ~1.2 us old by now)
+                    if (!params_loaded) {
+                        if (step == 0) PARAM_LOADS();
+                        else if (ready_seen < ready_need) ready_seen = ld_relaxed64(ready);
+                    }
                     const long long t0 = clock64();
                     unsigned spins = 0;
                     for (;;) {                                // re-issue everything still missing, together
@@ -636,7 +633,13 @@ train_persist_kernel(PersistArgs a) {
                             if (vf[i] != tl)
                                 asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx[i]), "=r"(vf[i])
                                              : "l"(p + (size_t)i * B * HID) : "memory");
+                        if (!params_loaded && ready_seen < ready_need) ready_seen = ld_relaxed64(ready);
                     }
+                    // this thread's polls are home: if last step's W2 / W3 / b2 updates have been published by now (the sample
+                    // travelled with the polls), request its share of the 72 KB here, BEHIND its polls (a poll queued
+                    // behind the 64 KB came back ~0.5 us later), so that they arrive while stage 1 runs.  (Requesting
+                    // CTA-wide after the barrier below instead: the sample is stale by then, 6.7 instead of 6.4 us/step.)
+                    if (!params_loaded && ready_seen >= ready_need) { PARAM_LOADS(); DBG_STAMP(14); }
                     b1v = __uint_as_float(bx);
                     if (row == cta) DBG_STAMP(15);
 #pragma unroll
@@ -649,7 +652,7 @@ train_persist_kernel(PersistArgs a) {
                 }
                 s.red[h * HID + j] = zp;
                 if (row == cta) DBG_STAMP(12);
-                if (!staged) { __pipeline_wait_prior(0); staged = true; }    // W3 / b2 (/ b1 at step 0) are in smem
+                if (!staged && step == 0) __pipeline_wait_prior(0);          // b1 of the launch's first step comes with W3 / b2
                 __syncthreads();
                 if (row == cta) DBG_STAMP(2);
                 DBG_STAMP(6);
@@ -660,6 +663,20 @@ train_persist_kernel(PersistArgs a) {
                     h1 = (z > 0.f && keep) ? z * scale : 0.f;
                     ll_store1(arow + ACT_H1D + j, tl, h1);
                     s.hs[j] = h1;
+                }
+                // W2 / W3 / b2 are first needed now.  Stage 1 above ran on the partial sums and b1 alone (they arrive
+                // ~0.4 us before the 'ready' count of last step's W2 / W3 / b2 updates shows); every thread now waits for
+                // the count itself and requests its share of the 72 KB (a request issued before the polls of stage 1 made
+                // them queue behind 64 KB: + 0.5 us).
+                if (!params_loaded) {
+                    const long long tr = clock64();
+                    unsigned rspins = 0;
+                    while (ready_seen < ready_need) {
+                        if (poll_miss(a.lerr, tr, rspins)) break;
+                        ready_seen = ld_relaxed64(ready);
+                    }
+                    PARAM_LOADS();
+                    DBG_STAMP(14);
                 }
                 __syncthreads();
                 // ---- 2. z2 = h1d . W2^T + b2 : 8x8 block products, reduced over the 16 column blocks
@@ -678,6 +695,7 @@ train_persist_kernel(PersistArgs a) {
                     *reinterpret_cast<float4*>(&red2[kb * RLD + jb * 8]) = make_float4(zr[0], zr[1], zr[2], zr[3]);
                     *reinterpret_cast<float4*>(&red2[kb * RLD + jb * 8 + 4]) = make_float4(zr[4], zr[5], zr[6], zr[7]);
                 }
+                if (!staged) { __pipeline_wait_prior(0); staged = true; }    // W3 / b2 are in smem behind the next barrier
                 __syncthreads();
                 bool gate2 = false;
                 if (h == 0) {
