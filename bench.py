@@ -267,7 +267,10 @@ def main() -> None:
     if not args.no_parity_gate and B <= 512:
         sys.path.insert(0, os.path.join(REPO, "tests"))
         import parity_gate
-        parity = parity_gate.run_gate(dev, rank, world, dist if world > 1 else None)
+        try:
+            parity = parity_gate.run_gate(dev, rank, world, dist if world > 1 else None)
+        except Exception as e:                               # the gate's machinery failed: say so, keep the line
+            parity = {"ok": False, "failures": [f"gate raised {e!r}"], "world_size": world}
         torch.cuda.synchronize()
 
     # ---- data: resident u8 dataset (same bytes on every rank), epoch-0 shard of this rank

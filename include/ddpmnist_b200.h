@@ -73,8 +73,10 @@ int ddpm_dropout_mask_philox(uint8_t* d_mask, int batch, uint64_t seed, uint64_t
 
 /* -------------------------------------------------------------------------------- fused step
  * Workspace: one caller-owned device buffer of ddpm_workspace_bytes(max_batch) bytes, 256-byte
- * aligned, reused by every step (activations, gates, split-K partials, two control words).
- * Call ddpm_workspace_init once after allocating it (it zeroes the control words; stream-ordered).
+ * aligned, reused by every step (control block, activations, gates, split-K partials, gradient slices, and the
+ * persistent kernel's tagged dataflow words: 8.3 MB at batch 64, 24.9 MB at 512, 78 MB at 4096).
+ * Call ddpm_workspace_init once after allocating it (it zeroes the control block and the tagged-word region - memory
+ * from a caching allocator may hold the tagged words of an earlier workspace; stream-ordered).
  * Contents between calls are meaningful only to ddpm_step_backward, which reads what the last
  * ddpm_step_forward on the same workspace left.  One workspace serves one stream at a time. */
 size_t ddpm_workspace_bytes(int max_batch);
@@ -180,7 +182,7 @@ int ddpm_workspace_error(const void* d_workspace, int* h_err);
  * (bit-identical replicas) and applies the SGD update in place.  No fences, no collective library
  * call and no kernel launch between steps.
  *
- * A communicator owns one symmetric device buffer (1.9 MB per rank of the job; besides a host feed's ring, below,
+ * A communicator owns one symmetric device buffer (2.0 MB per rank of the job; besides a host feed's ring, below,
  * the only device memory this library allocates) that every peer process maps with CUDA IPC.  One process per GPU, all GPUs in one
  * NVLink/P2P domain, world <= 8.  Set-up (host side, blocking):
  *   ddpm_comm_create(rank, world, &c)            on every rank (its GPU current)
