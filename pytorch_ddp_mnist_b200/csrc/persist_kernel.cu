@@ -18,8 +18,9 @@
 // barrier cost 3,800 cycles between A and B and 2,600 between B and C (release fence behind the CTA's stores +
 // atomic + poll, profiles/r02_*timeline*); a tagged word is visible one L2 hop after it was stored.  Buffers are
 // double-buffered by step parity: a producer can reach step t+2 only after every consumer of step t has finished
-// with it (each phase needs the output of ALL CTAs of the phase before).  Updated W2 / W3 / biases are published
-// through one monotonic counter (release by the 44 updating CTAs, polled by the row CTAs).
+// with it (each phase needs the output of ALL CTAs of the phase before).  The updated W2 / W3 / b2 are published
+// through one monotonic counter (release by their 36 owner CTAs, sampled by every thread of the row CTAs); the
+// updated b1 travels as tagged words.
 //
 // Every sum has a fixed order: results are bit-identical run to run and independent of timing.
 #include <cuda_pipeline.h>
@@ -521,8 +522,9 @@ train_persist_kernel(PersistArgs a) {
         // Row CTAs fetch this step's W2 (into registers: thread (jb, kb) keeps the 8x8 block W2[jb*8.., kb*8..], used by
         // both the forward product, reduced over kb, and the backward product, reduced over jb) and W3 / b2 (into smem)
         // once the 'ready' counter shows that the 36 owner CTAs finished last step's updates.  EVERY thread samples the
-        // counter itself (no broadcast, no barrier): at the top of the step, and again right after phase A, where the
-        // loads are issued.  (Tried, %globaltimer-stamped: looking at the sample INSIDE phase A and issuing the loads
+        // counter itself (no broadcast, no barrier): at the top of the step and again together with the partial-sum
+        // polls of stage 1; the loads are issued when the thread's polls are home (see there), else after stage 1.
+        // (Tried, %globaltimer-stamped: looking at the sample INSIDE phase A and issuing the loads
         // there - the 64 KB arrive earlier, but the loop around them takes 2,250 ns instead of 1,310 and the step time is
         // the same; a TMA bulk copy into smem issued by one thread - same result.  The chain that binds is
         // dz2 -> dW2 tiles -> release -> this fetch -> z2, profiles/r02_phase_timeline_1gpu_globaltimer.txt.)
