@@ -137,3 +137,24 @@ def test_streaming_synth_writer_equals_in_memory(tmp_path):
     a, b = cdf5.read_mnist_cdf5(p)
     assert np.array_equal(a, im) and np.array_equal(b, lb)
     assert np.bincount(im.ravel(), minlength=256).min() > 0      # every byte value occurs
+
+
+def test_parallel_synth_writer_is_byte_identical(tmp_path):
+    """bench.py --config scaled6m lets every rank (and a few worker processes per rank) write its share of the
+    100,000-sample chunks of the synthetic CDF-5 file: the result must be the very file the serial writer produces."""
+    import hashlib
+    from pytorch_ddp_mnist_b200 import synth
+    n, seed = 230_017, 99                                    # three chunks, the last one ragged
+    a, b = str(tmp_path / "serial.nc"), str(tmp_path / "parallel.nc")
+    synth.write_synth_file(a, n, seed)
+    synth.write_synth_file_part(b, n, seed, 0, 1, True)      # lay the file out
+    for part in (2, 0, 1):                                   # any order, any number of writers
+        synth.write_synth_file_part(b, n, seed, part, 3, False)
+    sha = lambda p: hashlib.sha256(open(p, "rb").read()).hexdigest()
+    assert sha(a) == sha(b)
+    import bench_scaled
+    c = str(tmp_path / "procs.nc")
+    synth.write_synth_file_part(c, n, seed, 0, 1, True)
+    bench_scaled._make_file(c, n, seed, 0, 2, procs=2)       # rank 0 of 2, two worker processes
+    bench_scaled._make_file(c, n, seed, 1, 2, procs=2)
+    assert sha(a) == sha(c)
