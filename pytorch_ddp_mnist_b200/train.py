@@ -46,6 +46,11 @@ def configure(argv=None):
             help="accepted in both spellings (torch.distributed.launch passes --local-rank; tg:123)")
     add_arg("--progress", type=int, default=0, help="refresh the progress line every N steps (0 = off)")
     add_arg("--seed", type=int, default=None, help="torch.manual_seed before create_model() (reference: unseeded)")
+    add_arg("--model", type=str, default="ref_mlp", choices=["ref_mlp", "json_convnet"],
+            help="ref_mlp = the reference's create_model() (default); json_convnet = the ConvNet BASELINE.json names "
+                 "(conv 1->32, conv 32->64, maxpool, fc 9216->128, fc 128->10; Adadelta lr 1.0, StepLR gamma 0.7) - "
+                 "NOT in the reference")
+    add_arg("--gamma", type=float, default=0.7, help="json_convnet only: StepLR(step_size=1) decay per epoch")
     args = parser.parse_args(argv)
 
     config = {"trainer": {}, "data": {}}
@@ -57,6 +62,8 @@ def configure(argv=None):
     config["trainer"]["num_workers"] = 0
     config["trainer"]["progress"] = args.progress
     config["trainer"]["seed"] = args.seed
+    config["trainer"]["model"] = args.model
+    config["trainer"]["gamma"] = args.gamma
     config["data"]["limit"] = None
     config["data"]["label_map"] = [0, 1, 0, 0, 2, 3, 1, 4]
     config["data"]["hdf5"] = args.hdf5
@@ -167,6 +174,37 @@ def main(model: nn.Module, train_loader: DeviceBatchLoader, test_loader: DeviceB
     return model
 
 
+def main_convnet(train_loader: DeviceBatchLoader, test_loader: DeviceBatchLoader, config):
+    """The recipe BASELINE.json describes for its ConvNet (NOT in the reference: there is nothing to cite; oracle =
+    oracle/convnet_oracle.py, parity unpinned): per epoch one pass over this rank's shard with Adadelta(lr=1.0), the
+    bucket all-reduced over NCCL at ws > 1, then the whole test set (loss + accuracy) on every rank and
+    `StepLR(step_size=1, gamma)`.  Same loaders, sampler and printed line shape as `main()`; returns the engine."""
+    from .convnet import ConvNetEngine, init_params_like_torch
+    rank = config["trainer"]["rank"]
+    world_size = config["trainer"].get("world_size", 1)
+    device = torch.device(config["trainer"]["device"])
+    batch = config["trainer"]["batch_size"]
+    eng = ConvNetEngine(device, batch, lr=1.0, world_size=world_size, rank=rank, tf32=True)
+    eng.load_state_dict(init_params_like_torch())
+    eng.broadcast_params(0)
+    train_res, test_res = train_loader.resident, test_loader.resident
+    for i in range(config["trainer"]["n_epochs"]):
+        train_loader.sampler.set_epoch(i)
+        eng.loss.zero_()
+        for idx in train_loader.index_batches():
+            eng.train_step(train_res, idx)
+        epoch_loss = float(eng.loss[1].item())
+        eng.loss.zero_()
+        correct, total = 0.0, 0
+        for idx in test_loader.index_batches():
+            correct += eng.accuracy(test_res, idx) * idx.numel()     # eval forward; accumulates loss[1] like mp:481
+            total += idx.numel()
+        val_loss = float(eng.loss[1].item())
+        print(f"Epoch={i}, train_loss={epoch_loss:.4f}, val_loss={val_loss:.4f}, val_acc={correct / max(total, 1):.4f}")
+        eng.scale_lr(config["trainer"].get("gamma", 0.7))
+    return eng
+
+
 def run(argv=None) -> None:
     """The reference's `__main__` block (mp:489-511)."""
     config = configure(argv)
@@ -176,6 +214,13 @@ def run(argv=None) -> None:
         torch.manual_seed(config["trainer"]["seed"])
     train_loader, test_loader = create_data_loaders(config, None, dataset_loc=config["data"]["path"],
                                                     device=config["trainer"]["device"])
+    if config["trainer"].get("model") == "json_convnet":
+        eng = main_convnet(train_loader, test_loader, config)
+        if rank == 0:
+            torch.save(eng.state_dict(), 'convnet.pt')
+        if comm is not None:
+            comm.finalize()
+        return
     model = main(model=create_model(), train_loader=train_loader, test_loader=test_loader, config=config)
     if rank == 0:
         torch.save({k: v.detach().cpu() for k, v in model.state_dict().items()}, 'model.pt')

@@ -252,6 +252,19 @@ def test_train_script_single_gpu(dev, nc_dir):
     assert list(sd.keys()) == list(O.PARAM_KEYS) and all(torch.isfinite(v).all() for v in sd.values())
 
 
+def test_train_script_convnet(dev, nc_dir):
+    """`python mnist_pnetcdf_b200.py --model json_convnet`: BASELINE.json's ConvNet recipe (Adadelta, StepLR, test
+    accuracy) through the same script, loaders and sampler - learns the synthetic classes and writes convnet.pt."""
+    out = _run_script(nc_dir, 1, extra=("--model", "json_convnet"))
+    lines = re.findall(r"Epoch=(\d+), train_loss=([0-9.]+), val_loss=([0-9.]+), val_acc=([0-9.]+)", out)
+    assert [l[0] for l in lines] == ["0", "1"], out[-2000:]
+    assert float(lines[1][2]) < float(lines[0][2]) or float(lines[1][3]) >= 0.99
+    assert float(lines[1][3]) > 0.9, lines
+    sd = torch.load(os.path.join(nc_dir, "convnet.pt"))
+    assert "conv1.weight" in sd and sd["fc1.weight"].shape == (128, 9216)
+    assert all(torch.isfinite(v).all() for v in sd.values())
+
+
 def test_train_script_two_gpus(dev, nc_dir):
     """Same script under torchrun on 2 GPUs (fused data-parallel step): every rank prints its epoch lines."""
     if torch.cuda.device_count() < 2:
